@@ -1,0 +1,199 @@
+/*
+ * henjou_b200.h — C ABI of libhenjou_b200.so, the B200-native (sm_100a) replacement for the
+ * device half of kinakomoti-321/Henjou-Renderer.
+ *
+ * What this boundary replaces in the reference (all paths relative to /root/reference):
+ *   - the device module loaded from `PTX_File.ptxfile_path` (HenjouRenderer/render_option.json:28-30,
+ *     include/renderer/renderer.h:508-519) exporting __raygen__rg / __miss__ms / __closesthit__ch /
+ *     __closesthit__shadow (renderer.h:528-573);
+ *   - the OptiX acceleration-structure calls buildGAS / buildIAS / updateIASMatrix
+ *     (renderer.h:319-490, 257-291);
+ *   - the launch itself: cudaMemcpy(Params) + optixLaunch(W,H,1) + sync (renderer.h:1229-1242);
+ *   - the AOV read-back + sRGB quantisation (renderer.h:73-101, 1279-1283).
+ *
+ * Plain C: pointers + sizes only, no C++/torch types. All input pointers are HOST pointers that are
+ * borrowed for the duration of the call (copied to the device inside). No exception crosses the ABI:
+ * every entry point returns HJ_OK (0) or a negative hj_status; hj_last_error() gives the message.
+ * A context is not thread-safe; it owns one CUDA stream and all of its device memory.
+ */
+#ifndef HENJOU_B200_H
+#define HENJOU_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HJ_ABI_VERSION 1
+
+typedef struct hj_ctx hj_ctx;
+
+typedef enum hj_status {
+    HJ_OK = 0,
+    HJ_ERR_INVALID = -1,   /* bad argument / inconsistent scene description      */
+    HJ_ERR_CUDA = -2,      /* a CUDA runtime call failed (message has the detail) */
+    HJ_ERR_NO_SCENE = -3,  /* hj_accel_build / hj_render before hj_scene_upload   */
+    HJ_ERR_NO_ACCEL = -4,  /* hj_render before hj_accel_build                     */
+    HJ_ERR_NO_FRAME = -5,  /* hj_readback before hj_render                        */
+    HJ_ERR_COMM = -6,      /* NCCL failure                                        */
+    HJ_ERR_OOM = -7        /* device allocation failed                            */
+} hj_status;
+
+/* rt.h:85 (Pathtrace), rt.h:162 (NEE), rt.h:284 (MIS). SURVEY decision D3: default MIS. */
+typedef enum hj_integrator { HJ_INTEGRATOR_PT = 0, HJ_INTEGRATOR_NEE = 1, HJ_INTEGRATOR_MIS = 2 } hj_integrator;
+
+/* kernel/color.h:10-63. SURVEY decision D7: default none (linear mean radiance in the colour AOV). */
+typedef enum hj_tonemap { HJ_TONEMAP_NONE = 0, HJ_TONEMAP_ACES = 1, HJ_TONEMAP_UCHIMURA = 2 } hj_tonemap;
+
+typedef enum hj_aov {
+    HJ_AOV_COLOR = 0,        /* float4[W*H]  Params::aov_color   (renderer.h:1222)                         */
+    HJ_AOV_ALBEDO = 1,       /* float4[W*H]  Params::aov_albedo  (renderer.h:1221)                         */
+    HJ_AOV_NORMAL = 2,       /* float4[W*H]  Params::aov_normal  (renderer.h:1223)                         */
+    HJ_AOV_RGBA8 = 3,        /* uchar4[W*H]  Params::image; float4ConvertColor semantics (renderer.h:87)   */
+    HJ_AOV_ACCUM = 4,        /* float4[W*H]  raw radiance SUM of this context's sample slice (multi-GPU)   */
+    HJ_AOV_PATH_RADIANCE = 5,/* float4[n_samples*W*H] debug: per-sample radiance rgb, w = #rays of path     */
+    HJ_AOV_PATH_IDS = 6      /* uint32[2*n_samples*W*H] debug: {first-hit global prim id | 0xffffffff,
+                                                               hash of every closest-hit id on the path}   */
+} hj_aov;
+
+typedef enum hj_accel_mode { HJ_ACCEL_BUILD = 0, HJ_ACCEL_REFIT = 1 } hj_accel_mode;
+
+/* Mirrors HitGroupData as filled by Renderer::optixSBTBuild (renderer.h:659-687) from
+ * Material (include/renderer/material.h:10-63). Texture ids index hj_scene_desc::textures, -1 = none. */
+typedef struct hj_material {
+    float basecolor[3];
+    int32_t basecolor_tex;
+    float emission[3];          /* already multiplied by KHR_materials_emissive_strength (gltfloader.h:1237-1245) */
+    int32_t emission_tex;       /* always -1 from the loader (gltfloader.h:1159); kept for layout parity */
+    int32_t is_light;
+    float metallic;
+    int32_t metallic_tex;       /* loader sets = roughness_tex (gltfloader.h:1156) */
+    float roughness;
+    int32_t roughness_tex;
+    float specular[3];
+    float sheen;
+    float clearcoat;
+    int32_t clearcoat_tex;
+    int32_t bump_tex;
+    int32_t normal_tex;
+    float transmission;
+    float ior;
+    int32_t ideal_specular;     /* roughness==0 && transmission>0 (gltfloader.h:1260-1263) */
+    int32_t is_thinfilm;
+} hj_material;
+
+/* Decoded 8-bit RGBA image as produced by Texture (include/renderer/texture.h:16-39). */
+typedef struct hj_texture {
+    const uint8_t* rgba8;       /* width*height*4 bytes, row 0 first */
+    int32_t width, height;
+    int32_t srgb;               /* 1: decode sRGB->linear on fetch (renderer.h:785-789), 0: NonColor */
+} hj_texture;
+
+/* The nine SceneData arrays (include/renderer/scene.h:19-37) + materials, textures, sky and LUT. */
+typedef struct hj_scene_desc {
+    const float* vertices;            /* float3[n_vertices], object space                          */
+    const float* normals;             /* float3[n_vertices]                                        */
+    const float* texcoords;           /* float2[n_vertices]                                        */
+    const uint32_t* indices;          /* uint32[3*n_triangles] (loader emits the identity)         */
+    const uint32_t* material_ids;     /* uint32[n_triangles]                                       */
+    const uint32_t* prim_offsets;     /* uint32[n_instances], first global triangle of instance i  */
+    uint32_t n_vertices, n_triangles, n_instances;
+    const hj_material* materials;
+    uint32_t n_materials;
+    const hj_texture* textures;
+    uint32_t n_textures;
+    const uint32_t* light_prim_ids;   /* ascending global triangle ids                             */
+    const float* light_prim_emission; /* float3[n_light_prims]                                     */
+    uint32_t n_light_prims;
+    const float* ibl_rgba32f;         /* float4[ibl_width*ibl_height]; 1x1 = constant sky (texture.h:58-65) */
+    int32_t ibl_width, ibl_height;
+    const uint8_t* lut_rgba8;         /* thin-film LUT, RGBA8, non-sRGB (renderer.h:854-898); may be NULL */
+    int32_t lut_width, lut_height;
+} hj_scene_desc;
+
+/* Params (renderer.h:1175-1227) minus the device pointers. */
+typedef struct hj_frame_params {
+    uint32_t width, height;
+    uint32_t spp;                 /* Params::spp — total samples per pixel of the frame (the normaliser)  */
+    uint32_t sample_begin;        /* this context renders global sample indices [sample_begin,sample_end) */
+    uint32_t sample_end;          /* single GPU: 0, spp                                                    */
+    uint32_t frame;               /* Params::frame — CMJ scramble                              */
+    float camera_pos[3];
+    float camera_dir[3];
+    float camera_up[3];
+    float camera_right[3];
+    float camera_f;               /* 2/tan(fov) (renderer.h:1147) */
+    float ibl_intensity;
+    int32_t integrator;           /* hj_integrator */
+    int32_t max_depth;            /* literal 10 in the reference (rt.h:89,166,288) */
+    int32_t tonemap;              /* hj_tonemap */
+    int32_t pixel_jitter;         /* 1 = first CMJ draw of each sample jitters the pixel */
+    int32_t debug_paths;          /* 1 = record HJ_AOV_PATH_* (needs n_samples*W*H*24 bytes) */
+    int32_t reserved;
+} hj_frame_params;
+
+typedef struct hj_stats {
+    uint64_t rays_extend;         /* closest-hit queries traced in the last hj_render (RayTrace, rt.h:43)      */
+    uint64_t rays_shadow;         /* occlusion queries traced (TraceOcculution, rt.h:15)                       */
+    uint64_t paths;               /* camera paths started                                                       */
+    uint64_t nodes_fetched;       /* BVH nodes fetched (only with hj_set_option("count_fetches",1))             */
+    uint64_t tris_fetched;        /* triangles fetched (same)                                                   */
+    uint64_t kernel_launches;     /* kernels launched by the last hj_render                                     */
+    float ms_render;              /* device time of the last hj_render (CUDA events on the ctx stream)          */
+    float ms_trace;               /* ... of which traversal kernels (only with option "time_stages")            */
+    float ms_shade;
+    float ms_accel;               /* device time of the last hj_accel_build                                     */
+    uint32_t bvh_nodes;           /* nodes in the current acceleration structure                                */
+    uint32_t bvh_node_bytes;      /* bytes per node                                                             */
+} hj_stats;
+
+int hj_abi_version(void);
+
+/* Creates a context on CUDA device `device`. Fails (HJ_ERR_CUDA) when no sm_100 device is present:
+ * there is no CPU fallback. */
+int hj_create(hj_ctx** out, int device);
+void hj_destroy(hj_ctx* ctx);
+const char* hj_last_error(const hj_ctx* ctx);   /* ctx may be NULL: last hj_create error */
+
+/* "count_fetches" 0|1, "time_stages" 0|1, "paths_per_pass" N (0 = auto), "wide_bvh" 0|1 */
+int hj_set_option(hj_ctx* ctx, const char* key, int64_t value);
+
+/* ≙ Renderer::cpySceneDataToDevice + textureBind + setSky + setLUT (renderer.h:197-255, 740-898). */
+int hj_scene_upload(hj_ctx* ctx, const hj_scene_desc* scene);
+
+/* ≙ buildGAS+buildIAS (mode BUILD) / updateIASMatrix (renderer.h:257-291).
+ * xforms3x4: n_instances row-major 3x4 instance-to-world matrices (Matrix4x3, include/cu/matrix_4x3.h:12);
+ * inv_xforms3x4: rows of the inverse (renderer.h:272-284), NULL = computed here. NULL xforms = identity. */
+int hj_accel_build(hj_ctx* ctx, const float* xforms3x4, const float* inv_xforms3x4, uint32_t n_instances, int mode);
+
+/* ≙ cudaMemcpy(Params) + optixLaunch + CUDA_SYNC_CHECK (renderer.h:1229-1242). Synchronous. */
+int hj_render(hj_ctx* ctx, const hj_frame_params* frame);
+
+/* Same as hj_render but returns right after enqueueing on the context stream (bench / overlap). */
+int hj_render_async(hj_ctx* ctx, const hj_frame_params* frame);
+int hj_sync(hj_ctx* ctx);
+
+/* Copies an AOV of the last rendered frame into caller memory; `bytes` must be the exact size. */
+int hj_readback(hj_ctx* ctx, int aov, void* dst, size_t bytes);
+
+/* Device address of an AOV buffer (for torch.distributed / zero-copy consumers); NULL if absent. */
+void* hj_device_ptr(hj_ctx* ctx, int aov);
+
+/* Re-runs normalise+tonemap+quantise from HJ_AOV_ACCUM (after an external reduction wrote into it). */
+int hj_finalize(hj_ctx* ctx);
+
+int hj_get_stats(hj_ctx* ctx, hj_stats* out);
+
+/* Multi-GPU: sample-slice data parallelism, replicated scene, one sum-reduction of the
+ * float4 accumulation buffer per frame over NCCL/NVLink. unique_id is the 128-byte ncclUniqueId. */
+int hj_comm_unique_id(void* unique_id_128);
+int hj_comm_init(hj_ctx* ctx, const void* unique_id_128, int rank, int nranks);
+/* all-reduces HJ_AOV_ACCUM over the communicator and finalises the colour/RGBA8 AOVs on every rank. */
+int hj_comm_reduce(hj_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HENJOU_B200_H */
