@@ -5,19 +5,12 @@
 // Local shading frame is y-up; "wo" is the direction back along the incoming ray.
 #pragma once
 #include "hjo_kernel.h"
+#include "hjo_trace.h"
 
 namespace hjo {
 
-// the scene the thread-local texture fetches read (set by the render entry points)
-struct ShadeCtx { const Scene* scene = nullptr; };
-static thread_local ShadeCtx g_shade;
-
 // disneyBRDF.h:11-14 — tex2D<float4>(params.lut_texture,u,v): RGBA8, wrap, bilinear, non-sRGB
-static inline float3 lut_fetch(float u, float v) {
-    const Scene* S = g_shade.scene;
-    if (!S || !S->has_lut) return make_float3(0.0f);
-    return make_float3(bilinear8(S->lut, u, v));
-}
+static inline float3 lut_fetch(float u, float v) { return lut_lookup(u, v); }
 
 // ------------------------------------------------------------------ DisneyBRDF (disneyBRDF.h:16-327)
 struct Disney {
