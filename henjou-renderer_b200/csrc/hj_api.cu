@@ -1,0 +1,296 @@
+// hj_api.cu — the C ABI of libhenjou_b200.so (include/henjou_b200.h): context, scene upload, option handling,
+// read-back. Replaces the host<->device plumbing of the reference's Renderer
+// (/root/reference/include/renderer/renderer.h: cpySceneDataToDevice :197-255, textureBind :740-800,
+// setSky :802-851, setLUT :854-898, updateIASMatrix :257-291, launch :1229-1242, AOV read-back :1279-1283).
+// No exception crosses the boundary; there is no CPU path: without an sm_100 device hj_create fails.
+#include "hj_ctx.h"
+#include <cmath>
+#include <cstring>
+#include <new>
+
+static std::string g_create_err;
+
+#define HJ_REQUIRE(ctx, cond, code, msg)            \
+    do { if (!(cond)) { (ctx)->err = (msg); return (code); } } while (0)
+
+template <class T>
+static int upload(hj_ctx* c, DevBuf& b, const T* src, size_t n) {
+    HJ_CUDA(c, b.reserve(std::max<size_t>(n, 1) * sizeof(T)));
+    if (n) HJ_CUDA(c, cudaMemcpyAsync(b.p, src, n * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+    return HJ_OK;
+}
+
+extern "C" {
+
+int hj_abi_version(void) { return HJ_ABI_VERSION; }
+
+const char* hj_last_error(const hj_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int hj_create(hj_ctx** out, int device) {
+    if (!out) { g_create_err = "hj_create: out is NULL"; return HJ_ERR_INVALID; }
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) { g_create_err = std::string("hj_create: no CUDA device (") + cudaGetErrorString(e) + "); there is no CPU fallback"; return HJ_ERR_CUDA; }
+    if (device < 0 || device >= n) { g_create_err = "hj_create: device index out of range"; return HJ_ERR_INVALID; }
+    cudaDeviceProp p;
+    if ((e = cudaGetDeviceProperties(&p, device)) != cudaSuccess) { g_create_err = cudaGetErrorString(e); return HJ_ERR_CUDA; }
+    if (p.major != 10) {
+        char b[200]; snprintf(b, sizeof b, "hj_create: device %d is sm_%d%d; this library contains sm_100a code only", device, p.major, p.minor);
+        g_create_err = b; return HJ_ERR_CUDA;
+    }
+    if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_err = cudaGetErrorString(e); return HJ_ERR_CUDA; }
+    hj_ctx* c = new (std::nothrow) hj_ctx();
+    if (!c) { g_create_err = "hj_create: out of host memory"; return HJ_ERR_OOM; }
+    c->device = device;
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess || (e = cudaEventCreate(&c->ev0)) != cudaSuccess ||
+        (e = cudaEventCreate(&c->ev1)) != cudaSuccess) {
+        g_create_err = cudaGetErrorString(e); delete c; return HJ_ERR_CUDA;
+    }
+    *out = c;
+    return HJ_OK;
+}
+
+void hj_comm_destroy_internal(hj_ctx* c);
+
+void hj_destroy(hj_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    hj_comm_destroy_internal(c);
+    DevBuf* bufs[] = {&c->d_vertices, &c->d_normals, &c->d_texcoords, &c->d_indices, &c->d_material_ids, &c->d_prim_offsets, &c->d_tri_inst,
+                      &c->d_xf, &c->d_inv_xf, &c->d_materials, &c->d_textures, &c->d_texels, &c->d_srgb, &c->d_light_ids, &c->d_light_em,
+                      &c->d_ibl, &c->d_lut, &c->d_tri_pos, &c->d_tri_attr,
+                      &c->bvh.keys, &c->bvh.keys_alt, &c->bvh.vals, &c->bvh.vals_alt, &c->bvh.block_hist, &c->bvh.blo, &c->bvh.bhi, &c->bvh.left,
+                      &c->bvh.right, &c->bvh.parent, &c->bvh.rfirst, &c->bvh.rlast, &c->bvh.flags, &c->bvh.bounds, &c->bvh.queue_a, &c->bvh.queue_b,
+                      &c->bvh.counters, &c->bvh.nodes, &c->bvh.btris,
+                      &c->wf.ray_o, &c->wf.ray_d, &c->wf.hit, &c->wf.thr, &c->wf.L, &c->wf.rng_depth, &c->wf.dbg, &c->wf.q_extend[0], &c->wf.q_extend[1],
+                      &c->wf.q_shadow, &c->wf.q_mis, &c->wf.sh_o, &c->wf.sh_d, &c->wf.sh_c, &c->wf.mi_o, &c->wf.mi_d, &c->wf.mi_a, &c->wf.mi_t, &c->wf.counters,
+                      &c->aov_color, &c->aov_albedo, &c->aov_normal, &c->aov_rgba8, &c->aov_accum, &c->aov_path_rad, &c->aov_path_ids};
+    for (DevBuf* b : bufs) b->release();
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
+    if (!c || !key) return HJ_ERR_INVALID;
+    if (!strcmp(key, "count_fetches")) c->opt_count_fetches = value != 0;
+    else if (!strcmp(key, "time_stages")) c->opt_time_stages = value != 0;
+    else if (!strcmp(key, "paths_per_pass")) c->opt_paths_per_pass = value;
+    else if (!strcmp(key, "leaf_max")) { HJ_REQUIRE(c, value >= 1 && value <= 4, HJ_ERR_INVALID, "hj_set_option: leaf_max must be 1..4"); c->opt_leaf_max = (int)value; }
+    else { c->err = std::string("hj_set_option: unknown option '") + key + "'"; return HJ_ERR_INVALID; }
+    return HJ_OK;
+}
+
+static float srgb_to_linear(float v) { return (v <= 0.04045f) ? v / 12.92f : powf((v + 0.055f) / 1.055f, 2.4f); }
+
+int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
+    if (!c) return HJ_ERR_INVALID;
+    HJ_REQUIRE(c, d && d->vertices && d->indices && d->material_ids && d->prim_offsets, HJ_ERR_INVALID, "hj_scene_upload: missing geometry arrays");
+    HJ_REQUIRE(c, d->n_instances > 0 && d->n_triangles > 0 && d->n_vertices > 0, HJ_ERR_INVALID, "hj_scene_upload: empty scene");
+    HJ_REQUIRE(c, d->n_materials > 0 && d->materials, HJ_ERR_INVALID, "hj_scene_upload: no materials");
+    HJ_REQUIRE(c, d->prim_offsets[0] == 0, HJ_ERR_INVALID, "hj_scene_upload: prim_offsets[0] must be 0");
+    for (uint32_t i = 1; i < d->n_instances; i++)
+        HJ_REQUIRE(c, d->prim_offsets[i] > d->prim_offsets[i - 1] && d->prim_offsets[i] < d->n_triangles, HJ_ERR_INVALID, "hj_scene_upload: prim_offsets must be strictly increasing and < n_triangles");
+    for (size_t i = 0; i < 3 * (size_t)d->n_triangles; i++)
+        HJ_REQUIRE(c, d->indices[i] < d->n_vertices, HJ_ERR_INVALID, "hj_scene_upload: vertex index out of range");
+    for (uint32_t i = 0; i < d->n_triangles; i++)
+        HJ_REQUIRE(c, d->material_ids[i] < d->n_materials, HJ_ERR_INVALID, "hj_scene_upload: material id out of range");
+    for (uint32_t i = 0; i < d->n_light_prims; i++)
+        HJ_REQUIRE(c, d->light_prim_ids && d->light_prim_emission && d->light_prim_ids[i] < d->n_triangles, HJ_ERR_INVALID, "hj_scene_upload: bad light primitive list");
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    c->have_scene = c->have_accel = c->have_frame = false;
+    c->bvh.have_topology = false;
+    int rc;
+    const size_t nv = d->n_vertices, nt = d->n_triangles;
+    if ((rc = upload(c, c->d_vertices, d->vertices, 3 * nv))) return rc;
+    {   // normals default to +y and uvs to 0 when absent (the loader always provides them, gltfloader.h:1460-1482)
+        std::vector<float> tmp;
+        if (!d->normals) { tmp.assign(3 * nv, 0.0f); for (size_t i = 0; i < nv; i++) tmp[3 * i + 1] = 1.0f; }
+        if ((rc = upload(c, c->d_normals, d->normals ? d->normals : tmp.data(), 3 * nv))) return rc;
+        HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (!d->texcoords) tmp.assign(2 * nv, 0.0f);
+        if ((rc = upload(c, c->d_texcoords, d->texcoords ? d->texcoords : tmp.data(), 2 * nv))) return rc;
+        HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    if ((rc = upload(c, c->d_indices, d->indices, 3 * nt))) return rc;
+    if ((rc = upload(c, c->d_material_ids, d->material_ids, nt))) return rc;
+    if ((rc = upload(c, c->d_prim_offsets, d->prim_offsets, (size_t)d->n_instances))) return rc;
+    std::vector<uint32_t> tri_inst(nt);
+    for (uint32_t i = 0; i < d->n_instances; i++) {
+        const uint32_t b = d->prim_offsets[i], e = (i + 1 < d->n_instances) ? d->prim_offsets[i + 1] : d->n_triangles;
+        for (uint32_t t = b; t < e; t++) tri_inst[t] = i;
+    }
+    if ((rc = upload(c, c->d_tri_inst, tri_inst.data(), nt))) return rc;
+    std::vector<DevMaterial> mats(d->n_materials);
+    for (uint32_t i = 0; i < d->n_materials; i++) {
+        const hj_material& m = d->materials[i]; DevMaterial& o = mats[i];
+        for (int k = 0; k < 3; k++) { o.basecolor[k] = m.basecolor[k]; o.emission[k] = m.emission[k]; }
+        o.basecolor_tex = m.basecolor_tex; o.is_light = m.is_light; o.metallic = m.metallic; o.roughness = m.roughness;
+        o.roughness_tex = m.roughness_tex; o.sheen = m.sheen; o.clearcoat = m.clearcoat; o.ior = m.ior; o.transmission = m.transmission;
+        o.flags = (m.ideal_specular ? 1 : 0) | (m.is_thinfilm ? 2 : 0);
+    }
+    if ((rc = upload(c, c->d_materials, mats.data(), mats.size()))) return rc;
+    // textures: one texel pool + descriptors
+    size_t texels = 0;
+    for (uint32_t i = 0; i < d->n_textures; i++) {
+        HJ_REQUIRE(c, d->textures && d->textures[i].rgba8 && d->textures[i].width > 0 && d->textures[i].height > 0, HJ_ERR_INVALID, "hj_scene_upload: bad texture");
+        texels += (size_t)d->textures[i].width * d->textures[i].height;
+    }
+    HJ_CUDA(c, c->d_texels.reserve(std::max<size_t>(texels, 1) * 4));
+    std::vector<DevTexture> texd(std::max<uint32_t>(d->n_textures, 1));
+    size_t off = 0;
+    for (uint32_t i = 0; i < d->n_textures; i++) {
+        const size_t n = (size_t)d->textures[i].width * d->textures[i].height;
+        HJ_CUDA(c, cudaMemcpyAsync(c->d_texels.as<uchar4>() + off, d->textures[i].rgba8, n * 4, cudaMemcpyHostToDevice, c->stream));
+        texd[i].px = c->d_texels.as<uchar4>() + off; texd[i].w = d->textures[i].width; texd[i].h = d->textures[i].height; texd[i].srgb = d->textures[i].srgb;
+        off += n;
+    }
+    if ((rc = upload(c, c->d_textures, texd.data(), texd.size()))) return rc;
+    float table[256];
+    for (int i = 0; i < 256; i++) table[i] = srgb_to_linear((float)i / 255.0f);   // sRGB EOTF per texel (renderer.h:785)
+    if ((rc = upload(c, c->d_srgb, table, (size_t)256))) return rc;
+    if ((rc = upload(c, c->d_light_ids, d->light_prim_ids, (size_t)d->n_light_prims))) return rc;
+    if ((rc = upload(c, c->d_light_em, d->light_prim_emission, 3 * (size_t)d->n_light_prims))) return rc;
+    const float black[4] = {0, 0, 0, 0};
+    int iw = 1, ih = 1;
+    if (d->ibl_rgba32f && d->ibl_width > 0 && d->ibl_height > 0) { iw = d->ibl_width; ih = d->ibl_height; if ((rc = upload(c, c->d_ibl, d->ibl_rgba32f, 4 * (size_t)iw * ih))) return rc; }
+    else if ((rc = upload(c, c->d_ibl, black, (size_t)4))) return rc;
+    const bool has_lut = d->lut_rgba8 && d->lut_width > 0 && d->lut_height > 0;
+    if (has_lut) { if ((rc = upload(c, c->d_lut, d->lut_rgba8, 4 * (size_t)d->lut_width * d->lut_height))) return rc; }
+    HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    DevScene& S = c->S;
+    S = DevScene{};
+    S.vertices = c->d_vertices.as<float>(); S.normals = c->d_normals.as<float>(); S.texcoords = c->d_texcoords.as<float>();
+    S.indices = c->d_indices.as<uint32_t>(); S.material_ids = c->d_material_ids.as<uint32_t>(); S.prim_offsets = c->d_prim_offsets.as<uint32_t>();
+    S.tri_inst = c->d_tri_inst.as<uint32_t>();
+    S.n_vertices = d->n_vertices; S.n_tris = d->n_triangles; S.n_instances = d->n_instances; S.n_materials = d->n_materials;
+    S.n_textures = d->n_textures; S.n_lights = d->n_light_prims;
+    S.materials = c->d_materials.as<DevMaterial>(); S.textures = c->d_textures.as<DevTexture>(); S.srgb_table = c->d_srgb.as<float>();
+    S.light_prim_ids = c->d_light_ids.as<uint32_t>(); S.light_prim_emission = c->d_light_em.as<float>();
+    S.ibl = c->d_ibl.as<float4>(); S.ibl_w = iw; S.ibl_h = ih;
+    S.lut = c->d_lut.as<uchar4>(); S.lut_w = has_lut ? d->lut_width : 0; S.lut_h = has_lut ? d->lut_height : 0; S.has_lut = has_lut;
+    c->have_scene = true;
+    return HJ_OK;
+}
+
+// General 3x4 affine inverse by cofactors in float (the reference uses glm::inverse on the 4x4, renderer.h:272-284)
+static void invert_affine(const float* m, float* r) {
+    const float a = m[0], b = m[1], cc = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+    const float A = e * i - f * h, B = -(d * i - f * g), C = d * h - e * g;
+    const float det = a * A + b * B + cc * C;
+    const float id = 1.0f / det;
+    r[0] = A * id; r[1] = -(b * i - cc * h) * id; r[2] = (b * f - cc * e) * id;
+    r[4] = B * id; r[5] = (a * i - cc * g) * id; r[6] = -(a * f - cc * d) * id;
+    r[8] = C * id; r[9] = -(a * h - b * g) * id; r[10] = (a * e - b * d) * id;
+    const float tx = m[3], ty = m[7], tz = m[11];
+    r[3] = -(r[0] * tx + r[1] * ty + r[2] * tz);
+    r[7] = -(r[4] * tx + r[5] * ty + r[6] * tz);
+    r[11] = -(r[8] * tx + r[9] * ty + r[10] * tz);
+}
+
+int hj_accel_build(hj_ctx* c, const float* xf, const float* inv_xf, uint32_t n_instances, int mode) {
+    if (!c) return HJ_ERR_INVALID;
+    HJ_REQUIRE(c, c->have_scene, HJ_ERR_NO_SCENE, "hj_accel_build: no scene uploaded");
+    HJ_REQUIRE(c, n_instances == c->S.n_instances, HJ_ERR_INVALID, "hj_accel_build: n_instances differs from the uploaded scene");
+    HJ_REQUIRE(c, mode == HJ_ACCEL_BUILD || mode == HJ_ACCEL_REFIT, HJ_ERR_INVALID, "hj_accel_build: unknown mode");
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    std::vector<float> m(12 * (size_t)n_instances), im(12 * (size_t)n_instances);
+    for (uint32_t i = 0; i < n_instances; i++) {
+        float* p = &m[12 * (size_t)i]; float* q = &im[12 * (size_t)i];
+        if (xf) memcpy(p, xf + 12 * (size_t)i, 48);
+        else { memset(p, 0, 48); p[0] = p[5] = p[10] = 1.0f; }
+        if (inv_xf) memcpy(q, inv_xf + 12 * (size_t)i, 48);
+        else if (xf) invert_affine(p, q);
+        else memcpy(q, p, 48);
+    }
+    int rc;
+    if ((rc = upload(c, c->d_xf, m.data(), m.size()))) return rc;
+    if ((rc = upload(c, c->d_inv_xf, im.data(), im.size()))) return rc;
+    HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->S.xf = c->d_xf.as<float4>(); c->S.inv_xf = c->d_inv_xf.as<float4>();
+    c->have_accel = false;
+    if ((rc = hj_bvh_build(c, mode))) return rc;
+    c->have_accel = true;
+    return HJ_OK;
+}
+
+int hj_render_async(hj_ctx* c, const hj_frame_params* fp) {
+    if (!c || !fp) return HJ_ERR_INVALID;
+    HJ_REQUIRE(c, c->have_scene, HJ_ERR_NO_SCENE, "hj_render: no scene uploaded");
+    HJ_REQUIRE(c, c->have_accel, HJ_ERR_NO_ACCEL, "hj_render: hj_accel_build has not been called");
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    return hj_wavefront_render(c, fp);
+}
+
+int hj_sync(hj_ctx* c) {
+    if (!c) return HJ_ERR_INVALID;
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    HJ_CUDA(c, cudaGetLastError());
+    return c->have_frame ? hj_wavefront_stats(c) : HJ_OK;
+}
+
+int hj_render(hj_ctx* c, const hj_frame_params* fp) {
+    int rc = hj_render_async(c, fp);
+    return rc ? rc : hj_sync(c);
+}
+
+static int aov_info(hj_ctx* c, int aov, void** p, size_t* bytes) {
+    const size_t wh = (size_t)c->fp.width * c->fp.height, ns = c->fp.sample_end - c->fp.sample_begin;
+    switch (aov) {
+        case HJ_AOV_COLOR: *p = c->aov_color.p; *bytes = wh * 16; return HJ_OK;
+        case HJ_AOV_ALBEDO: *p = c->aov_albedo.p; *bytes = wh * 16; return HJ_OK;
+        case HJ_AOV_NORMAL: *p = c->aov_normal.p; *bytes = wh * 16; return HJ_OK;
+        case HJ_AOV_RGBA8: *p = c->aov_rgba8.p; *bytes = wh * 4; return HJ_OK;
+        case HJ_AOV_ACCUM: *p = c->aov_accum.p; *bytes = wh * 16; return HJ_OK;
+        case HJ_AOV_PATH_RADIANCE: *p = c->fp.debug_paths ? c->aov_path_rad.p : nullptr; *bytes = ns * wh * 16; return HJ_OK;
+        case HJ_AOV_PATH_IDS: *p = c->fp.debug_paths ? c->aov_path_ids.p : nullptr; *bytes = ns * wh * 8; return HJ_OK;
+    }
+    return HJ_ERR_INVALID;
+}
+
+int hj_readback(hj_ctx* c, int aov, void* dst, size_t bytes) {
+    if (!c || !dst) return HJ_ERR_INVALID;
+    HJ_REQUIRE(c, c->have_frame, HJ_ERR_NO_FRAME, "hj_readback: nothing rendered yet");
+    void* p = nullptr; size_t want = 0;
+    HJ_REQUIRE(c, aov_info(c, aov, &p, &want) == HJ_OK, HJ_ERR_INVALID, "hj_readback: unknown AOV");
+    HJ_REQUIRE(c, p != nullptr, HJ_ERR_INVALID, "hj_readback: AOV not recorded (debug_paths was 0)");
+    HJ_REQUIRE(c, bytes == want, HJ_ERR_INVALID, "hj_readback: size mismatch");
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    HJ_CUDA(c, cudaMemcpyAsync(dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    return HJ_OK;
+}
+
+void* hj_device_ptr(hj_ctx* c, int aov) {
+    if (!c || !c->have_frame) return nullptr;
+    void* p = nullptr; size_t b = 0;
+    return aov_info(c, aov, &p, &b) == HJ_OK ? p : nullptr;
+}
+
+int hj_finalize(hj_ctx* c) {
+    if (!c) return HJ_ERR_INVALID;
+    HJ_REQUIRE(c, c->have_frame, HJ_ERR_NO_FRAME, "hj_finalize: nothing rendered yet");
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    int rc = hj_wavefront_finalize(c);
+    if (rc) return rc;
+    HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    return HJ_OK;
+}
+
+int hj_get_stats(hj_ctx* c, hj_stats* out) {
+    if (!c || !out) return HJ_ERR_INVALID;
+    *out = c->stats;
+    return HJ_OK;
+}
+
+int hj_trace(hj_ctx* c, const float* rays, uint64_t n, int any_hit, uint32_t* prim, float* tuv) {
+    if (!c || (n && !rays)) return HJ_ERR_INVALID;
+    HJ_REQUIRE(c, c->have_accel, HJ_ERR_NO_ACCEL, "hj_trace: hj_accel_build has not been called");
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    return hj_trace_batch(c, rays, n, any_hit, prim, tuv);
+}
+
+}  // extern "C"

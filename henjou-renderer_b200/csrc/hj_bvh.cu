@@ -1,0 +1,434 @@
+// hj_bvh.cu — GPU acceleration-structure build: the B200 replacement for the reference's optixAccelBuild call
+// sites buildGAS / buildIAS / updateIASMatrix (/root/reference/include/renderer/renderer.h:319-396, 398-490,
+// 257-291). The loader emits one instance per mesh node with no hierarchy (gltfloader.h:1508-1512), so the
+// two-level GAS/IAS is flattened to world space each frame (semantics-preserving) and ONE
+// BVH is built over all triangles:
+//   k_flatten      instance transform -> world positions / normalised normals / uv / material per triangle
+//   k_morton       63-bit Morton code of the triangle centroid inside the scene bounds
+//   radix sort     hand-written LSD radix sort, 8 bits per pass, (u64 key, u32 value) pairs
+//   k_karras       binary radix tree (Karras 2012)
+//   k_fit          bottom-up AABB fit
+//   k_collapse     level-by-level collapse to 8-wide nodes with 8-bit quantised child boxes (80 B / node)
+#include "hj_ctx.h"
+#include "hj_trace.cuh"
+
+#define RS_THREADS 256
+#define RS_ITEMS 16
+#define RS_TILE (RS_THREADS * RS_ITEMS)
+
+// ---------------------------------------------------------------------------------------------- flatten
+// order-preserving float <-> int so atomicMin/atomicMax work on floats
+HJ_DI int f2ord(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+HJ_DI float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+__global__ void k_init_bounds(int* b) {
+    if (threadIdx.x < 3) b[threadIdx.x] = 0x7fffffff;
+    else if (threadIdx.x < 6) b[threadIdx.x] = (int)0x80000000;
+}
+
+// ≙ the vertex fetch + transform of __closesthit__ch (stale PTX :880-1287) hoisted out of the hit program:
+// p_k = transform_position(transforms[inst], vertices[i_k]); n_k = normalize(transform_normal(inv[inst], normals[i_k]))
+__global__ void k_flatten(DevScene S, int* bounds) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    if (t < S.n_tris) {
+        const uint32_t inst = S.tri_inst[t];
+        const float4* m = S.xf + 3 * (size_t)inst; const float4* im = S.inv_xf + 3 * (size_t)inst;
+        float3 p[3], n[3]; float2 uv[3];
+        for (int k = 0; k < 3; k++) {
+            const uint32_t vi = S.indices[3 * (size_t)t + k];
+            p[k] = xform_point(m, ld3(S.vertices, vi));
+            n[k] = normalize(xform_normal(im, ld3(S.normals, vi)));
+            uv[k] = make_float2(S.texcoords[2 * (size_t)vi], S.texcoords[2 * (size_t)vi + 1]);
+            lo[0] = fminf(lo[0], p[k].x); lo[1] = fminf(lo[1], p[k].y); lo[2] = fminf(lo[2], p[k].z);
+            hi[0] = fmaxf(hi[0], p[k].x); hi[1] = fmaxf(hi[1], p[k].y); hi[2] = fmaxf(hi[2], p[k].z);
+        }
+        float4* P = S.tri_pos + 3 * (size_t)t;
+        P[0] = f4(p[0], 0.0f); P[1] = f4(p[1], 0.0f); P[2] = f4(p[2], 0.0f);
+        float4* A = S.tri_attr + 4 * (size_t)t;
+        A[0] = f4(n[0], uv[0].x); A[1] = f4(n[1], uv[0].y); A[2] = f4(n[2], uv[1].x);
+        A[3] = make_float4(uv[1].y, uv[2].x, uv[2].y, __uint_as_float(S.material_ids[t]));
+    }
+    // block reduction of the scene bounds, one atomic per warp
+    for (int a = 0; a < 3; a++) {
+        float l = lo[a], h = hi[a];
+        for (int o = 16; o; o >>= 1) { l = fminf(l, __shfl_xor_sync(0xffffffffu, l, o)); h = fmaxf(h, __shfl_xor_sync(0xffffffffu, h, o)); }
+        if ((threadIdx.x & 31) == 0 && l <= h) { atomicMin(bounds + a, f2ord(l)); atomicMax(bounds + 3 + a, f2ord(h)); }
+    }
+}
+
+HJ_DI uint64_t spread21(uint32_t v) {
+    uint64_t x = v & 0x1fffffu;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void k_morton(DevScene S, const int* bounds, uint64_t* keys, uint32_t* vals) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= S.n_tris) return;
+    const float3 lo = f3(ord2f(bounds[0]), ord2f(bounds[1]), ord2f(bounds[2]));
+    const float3 hi = f3(ord2f(bounds[3]), ord2f(bounds[4]), ord2f(bounds[5]));
+    const float4* P = S.tri_pos + 3 * (size_t)t;
+    const float3 a = f3(P[0]), b = f3(P[1]), c = f3(P[2]);
+    const float3 cen = f3(fminf(a.x, fminf(b.x, c.x)) + fmaxf(a.x, fmaxf(b.x, c.x)), fminf(a.y, fminf(b.y, c.y)) + fmaxf(a.y, fmaxf(b.y, c.y)),
+                          fminf(a.z, fminf(b.z, c.z)) + fmaxf(a.z, fmaxf(b.z, c.z))) * 0.5f;
+    const float ex = fmaxf(hi.x - lo.x, 1e-30f), ey = fmaxf(hi.y - lo.y, 1e-30f), ez = fmaxf(hi.z - lo.z, 1e-30f);
+    const float e = fmaxf(ex, fmaxf(ey, ez));   // cubic cells: one scale for all axes
+    const uint32_t qx = (uint32_t)fminf(fmaxf((cen.x - lo.x) / e * 2097152.0f, 0.0f), 2097151.0f);
+    const uint32_t qy = (uint32_t)fminf(fmaxf((cen.y - lo.y) / e * 2097152.0f, 0.0f), 2097151.0f);
+    const uint32_t qz = (uint32_t)fminf(fmaxf((cen.z - lo.z) / e * 2097152.0f, 0.0f), 2097151.0f);
+    keys[t] = (spread21(qx) << 2) | (spread21(qy) << 1) | spread21(qz);
+    vals[t] = t;
+}
+
+// ---------------------------------------------------------------------------------------------- radix sort
+// One pass = histogram / scan / scatter. Warp w of a block owns a contiguous chunk of the tile, so a stable
+// rank is (elements of the same digit in earlier chunks) + (same digit earlier in this warp's chunk).
+__global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const uint64_t* __restrict__ keys, uint32_t n, int shift, uint32_t* __restrict__ block_hist, uint32_t nb) {
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * RS_TILE;
+    for (int i = 0; i < RS_ITEMS; i++) {
+        const uint32_t idx = base + i * RS_THREADS + threadIdx.x;
+        if (idx < n) atomicAdd(&h[(uint32_t)(keys[idx] >> shift) & 0xffu], 1u);
+    }
+    __syncthreads();
+    block_hist[threadIdx.x * nb + blockIdx.x] = h[threadIdx.x];
+}
+
+// exclusive scan of `len` counters in place, one block
+__global__ void __launch_bounds__(1024) k_rs_scan(uint32_t* a, uint32_t len) {
+    __shared__ uint32_t part[1024];
+    const uint32_t per = (len + 1023u) / 1024u;
+    const uint32_t b = min(threadIdx.x * per, len), e = min(b + per, len);
+    uint32_t s = 0;
+    for (uint32_t i = b; i < e; i++) s += a[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        uint32_t v = (threadIdx.x >= (uint32_t)o) ? part[threadIdx.x - o] : 0u;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    uint32_t run = part[threadIdx.x] - s;
+    for (uint32_t i = b; i < e; i++) { uint32_t v = a[i]; a[i] = run; run += v; }
+}
+
+__global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, uint32_t n, int shift,
+                                                           const uint32_t* __restrict__ block_off, uint32_t nb,
+                                                           uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
+    __shared__ uint32_t wh[RS_THREADS / 32][256];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < (RS_THREADS / 32) * 256; i += RS_THREADS) (&wh[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * RS_TILE + w * (32 * RS_ITEMS);
+    uint64_t k[RS_ITEMS]; uint32_t rank[RS_ITEMS];
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+        const uint32_t idx = base + i * 32 + lane;
+        const bool ok = idx < n;
+        k[i] = ok ? keys[idx] : ~0ull;
+        const uint32_t d = ok ? ((uint32_t)(k[i] >> shift) & 0xffu) : 256u;
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t before = __popc(peers & ((1u << lane) - 1u));
+        uint32_t cnt = 0;
+        if (ok) cnt = wh[w][d];
+        __syncwarp();
+        if (ok && before == 0) wh[w][d] = cnt + __popc(peers);
+        __syncwarp();
+        rank[i] = cnt + before;
+    }
+    __syncthreads();
+    {   // digit = threadIdx.x: turn per-warp counts into global write offsets
+        const int d = threadIdx.x;
+        uint32_t run = block_off[d * nb + blockIdx.x];
+        for (int ww = 0; ww < RS_THREADS / 32; ww++) { uint32_t c = wh[ww][d]; wh[ww][d] = run; run += c; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+        const uint32_t idx = base + i * 32 + lane;
+        if (idx < n) {
+            const uint32_t d = (uint32_t)(k[i] >> shift) & 0xffu;
+            const uint32_t pos = wh[w][d] + rank[i];
+            keys_out[pos] = k[i];
+            vals_out[pos] = vals[idx];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- Karras 2012
+// common-prefix length of sorted keys i and j; duplicates are disambiguated by the index
+HJ_DI int delta(const uint64_t* __restrict__ k, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint64_t a = k[i], b = k[j];
+    if (a == b) return 64 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clzll((long long)(a ^ b));
+}
+
+// internal node i in [0,N-1); node ids: internal i -> i, leaf j -> N-1+j
+__global__ void k_karras(const uint64_t* __restrict__ keys, int n, uint32_t* left, uint32_t* right, uint32_t* parent, uint32_t* rfirst, uint32_t* rlast) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1) if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    const uint32_t L = (lo == gamma) ? (uint32_t)(n - 1 + gamma) : (uint32_t)gamma;
+    const uint32_t R = (hi == gamma + 1) ? (uint32_t)(n - 1 + gamma + 1) : (uint32_t)(gamma + 1);
+    left[i] = L; right[i] = R; parent[L] = (uint32_t)i; parent[R] = (uint32_t)i;
+    rfirst[i] = (uint32_t)lo; rlast[i] = (uint32_t)hi;
+    if (i == 0) parent[0] = 0xffffffffu;
+}
+
+__global__ void k_fit(const DevScene S, const uint32_t* __restrict__ sorted, int n, const uint32_t* __restrict__ left, const uint32_t* __restrict__ right,
+                      const uint32_t* __restrict__ parent, uint32_t* flags, float4* blo, float4* bhi) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const float4* P = S.tri_pos + 3 * (size_t)sorted[j];
+    const float3 a = f3(P[0]), b = f3(P[1]), c = f3(P[2]);
+    float3 lo = f3(fminf(a.x, fminf(b.x, c.x)), fminf(a.y, fminf(b.y, c.y)), fminf(a.z, fminf(b.z, c.z)));
+    float3 hi = f3(fmaxf(a.x, fmaxf(b.x, c.x)), fmaxf(a.y, fmaxf(b.y, c.y)), fmaxf(a.z, fmaxf(b.z, c.z)));
+    uint32_t id = (uint32_t)(n - 1 + j);
+    blo[id] = f4(lo, 0.0f); bhi[id] = f4(hi, 0.0f);
+    if (n == 1) return;
+    uint32_t p = parent[id];
+    while (p != 0xffffffffu) {
+        __threadfence();
+        if (atomicAdd(&flags[p], 1u) == 0u) return;     // the sibling subtree is not finished: it will carry on
+        const uint32_t l = left[p], r = right[p];
+        const float4 ll = __ldcg(blo + l), lh = __ldcg(bhi + l), rl = __ldcg(blo + r), rh = __ldcg(bhi + r);   // L2 loads: written by other SMs
+        lo = f3(fminf(ll.x, rl.x), fminf(ll.y, rl.y), fminf(ll.z, rl.z));
+        hi = f3(fmaxf(lh.x, rh.x), fmaxf(lh.y, rh.y), fmaxf(lh.z, rh.z));
+        blo[p] = f4(lo, 0.0f); bhi[p] = f4(hi, 0.0f);
+        p = parent[p];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- collapse to 8-wide
+struct CollapseArgs {
+    int n; uint32_t leaf_max;
+    const uint32_t *left, *right, *rfirst, *rlast, *sorted;
+    const float4 *blo, *bhi;
+    const float4* tri_pos;
+    uint4* nodes; float4* btris;
+    uint32_t* counters;     // [0] nodes allocated, [1] triangles allocated, [2] next-level queue length
+};
+
+HJ_DI uint32_t bn_count(const CollapseArgs& a, uint32_t id) { return id >= (uint32_t)(a.n - 1) ? 1u : a.rlast[id] - a.rfirst[id] + 1u; }
+HJ_DI uint32_t bn_first(const CollapseArgs& a, uint32_t id) { return id >= (uint32_t)(a.n - 1) ? id - (uint32_t)(a.n - 1) : a.rfirst[id]; }
+HJ_DI float bn_area(const CollapseArgs& a, uint32_t id) {
+    const float4 l = a.blo[id], h = a.bhi[id];
+    const float dx = h.x - l.x, dy = h.y - l.y, dz = h.z - l.z;
+    return dx * dy + dy * dz + dz * dx;
+}
+
+// One thread turns one binary subtree root into one wide node: repeatedly opens the child with the largest
+// surface area until 8 children (or nothing left to open), orders the children into octant slots, quantises
+// their boxes conservatively on the node's 8-bit grid and copies the triangles of its leaf children.
+__global__ void k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32_t n_in, uint2* __restrict__ qout) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_in) return;
+    const uint2 work = qin[i];
+    uint32_t ch[8]; int nc = 1; ch[0] = work.x;
+    while (nc < 8) {
+        int best = -1; float ba = -1.0f;
+        for (int k = 0; k < nc; k++) {
+            const uint32_t id = ch[k];
+            const bool open = id < (uint32_t)(a.n - 1) && (bn_count(a, id) > a.leaf_max || nc == 1);
+            if (open) { const float ar = bn_area(a, id); if (ar > ba) { ba = ar; best = k; } }
+        }
+        if (best < 0) break;
+        const uint32_t id = ch[best];
+        ch[best] = a.left[id]; ch[nc++] = a.right[id];
+    }
+    // node box
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    float clo[8][3], chi[8][3];
+    for (int k = 0; k < nc; k++) {
+        const float4 l = a.blo[ch[k]], h = a.bhi[ch[k]];
+        clo[k][0] = l.x; clo[k][1] = l.y; clo[k][2] = l.z; chi[k][0] = h.x; chi[k][1] = h.y; chi[k][2] = h.z;
+        for (int ax = 0; ax < 3; ax++) { lo[ax] = fminf(lo[ax], clo[k][ax]); hi[ax] = fmaxf(hi[ax], chi[k][ax]); }
+    }
+    // octant slots: greedy assignment maximising (child centre - node centre) . (+-1,+-1,+-1)
+    int slot_of[8]; bool slot_used[8], child_done[8];
+    for (int k = 0; k < 8; k++) { slot_used[k] = false; child_done[k] = false; slot_of[k] = -1; }
+    for (int round = 0; round < nc; round++) {
+        float bc = -FLT_MAX; int bk = -1, bs = -1;
+        for (int k = 0; k < nc; k++) {
+            if (child_done[k]) continue;
+            float c[3];
+            for (int ax = 0; ax < 3; ax++) c[ax] = (clo[k][ax] + chi[k][ax]) * 0.5f - (lo[ax] + hi[ax]) * 0.5f;
+            for (int s = 0; s < 8; s++) {
+                if (slot_used[s]) continue;
+                const float cost = ((s & 1) ? c[0] : -c[0]) + ((s & 2) ? c[1] : -c[1]) + ((s & 4) ? c[2] : -c[2]);
+                if (cost > bc) { bc = cost; bk = k; bs = s; }
+            }
+        }
+        slot_of[bk] = bs; slot_used[bs] = true; child_done[bk] = true;
+    }
+    int child_in_slot[8];
+    for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
+    for (int k = 0; k < nc; k++) child_in_slot[slot_of[k]] = k;
+    // grid: per axis the smallest power-of-two step with 255 steps covering the node
+    uint32_t eb[3]; float scale[3];
+    for (int ax = 0; ax < 3; ax++) {
+        const float ext = hi[ax] - lo[ax];
+        uint32_t e = 1;
+        if (ext > 0.0f) {
+            const uint32_t bits = __float_as_uint(ext / 255.0f);
+            e = (bits >> 23) & 0xffu;
+            if (bits & 0x7fffffu) e++;
+            if (e < 1u) e = 1u;
+        }
+        while (e < 254u && lo[ax] + 255.0f * __uint_as_float(e << 23) < hi[ax]) e++;
+        eb[ax] = e; scale[ax] = __uint_as_float(e << 23);
+    }
+    uint32_t imask = 0, n_int = 0, n_tri = 0;
+    uint32_t meta[8], qlo[3][8], qhi[3][8];
+    for (int s = 0; s < 8; s++) {
+        meta[s] = 0;
+        for (int ax = 0; ax < 3; ax++) { qlo[ax][s] = 255; qhi[ax][s] = 0; }
+        const int k = child_in_slot[s];
+        if (k < 0) continue;
+        const uint32_t id = ch[k];
+        const uint32_t cnt = bn_count(a, id);
+        if (id < (uint32_t)(a.n - 1) && cnt > a.leaf_max) { imask |= 1u << s; n_int++; }
+        else { meta[s] = (cnt << 5) | n_tri; n_tri += cnt; }
+        for (int ax = 0; ax < 3; ax++) {
+            int ql = (int)floorf((clo[k][ax] - lo[ax]) / scale[ax]);
+            ql = max(0, min(255, ql));
+            while (ql > 0 && lo[ax] + (float)ql * scale[ax] > clo[k][ax]) ql--;
+            int qh = (int)ceilf((chi[k][ax] - lo[ax]) / scale[ax]);
+            qh = max(0, min(255, qh));
+            while (qh < 255 && lo[ax] + (float)qh * scale[ax] < chi[k][ax]) qh++;
+            qlo[ax][s] = (uint32_t)ql; qhi[ax][s] = (uint32_t)qh;
+        }
+    }
+    const uint32_t child_base = n_int ? atomicAdd(&a.counters[0], n_int) : 0u;
+    const uint32_t tri_base = n_tri ? atomicAdd(&a.counters[1], n_tri) : 0u;
+    // write the node
+    auto pack4 = [](const uint32_t* v) { return v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24); };
+    uint4* N = a.nodes + 5 * (size_t)work.y;
+    N[0] = make_uint4(__float_as_uint(lo[0]), __float_as_uint(lo[1]), __float_as_uint(lo[2]), eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24));
+    N[1] = make_uint4(child_base, tri_base, pack4(meta), pack4(meta + 4));
+    N[2] = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
+    N[3] = make_uint4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
+    N[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
+    // children: queue the internal ones (contiguous, in slot order), copy the triangles of the leaves
+    const uint32_t qbase = n_int ? atomicAdd(&a.counters[2], n_int) : 0u;
+    uint32_t r = 0;
+    for (int s = 0; s < 8; s++) {
+        const int k = child_in_slot[s];
+        if (k < 0) continue;
+        if (imask & (1u << s)) { qout[qbase + r] = make_uint2(ch[k], child_base + r); r++; }
+        else {
+            const uint32_t first = bn_first(a, ch[k]), cnt = meta[s] >> 5, off = meta[s] & 31u;
+            for (uint32_t j = 0; j < cnt; j++) {
+                const uint32_t prim = a.sorted[first + j];
+                const float4* P = a.tri_pos + 3 * (size_t)prim;
+                float4* T = a.btris + 3 * (size_t)(tri_base + off + j);
+                float4 v0 = P[0]; v0.w = __uint_as_float(prim);
+                T[0] = v0; T[1] = P[1]; T[2] = P[2];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- host driver
+static inline uint32_t cdiv(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
+
+int hj_bvh_build(hj_ctx* c, int mode) {
+    const uint32_t n = c->S.n_tris;
+    if (n == 0) { c->err = "hj_accel_build: scene has no triangles"; return HJ_ERR_INVALID; }
+    BvhState& B = c->bvh;
+    cudaStream_t st = c->stream;
+    HJ_CUDA(c, c->d_tri_pos.reserve(3 * (size_t)n * sizeof(float4)));
+    HJ_CUDA(c, c->d_tri_attr.reserve(4 * (size_t)n * sizeof(float4)));
+    HJ_CUDA(c, B.bounds.reserve(8 * sizeof(int)));
+    c->S.tri_pos = c->d_tri_pos.as<float4>(); c->S.tri_attr = c->d_tri_attr.as<float4>();
+    HJ_CUDA(c, cudaEventRecord(c->ev0, st));
+    k_init_bounds<<<1, 32, 0, st>>>(B.bounds.as<int>());
+    k_flatten<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.bounds.as<int>());
+    const bool topo = (mode == HJ_ACCEL_BUILD) || !B.have_topology;
+    if (topo) {
+        const uint32_t nb = cdiv(n, RS_TILE);
+        HJ_CUDA(c, B.keys.reserve((size_t)n * 8)); HJ_CUDA(c, B.keys_alt.reserve((size_t)n * 8));
+        HJ_CUDA(c, B.vals.reserve((size_t)n * 4)); HJ_CUDA(c, B.vals_alt.reserve((size_t)n * 4));
+        HJ_CUDA(c, B.block_hist.reserve((size_t)256 * nb * 4));
+        HJ_CUDA(c, B.left.reserve((size_t)n * 4)); HJ_CUDA(c, B.right.reserve((size_t)n * 4));
+        HJ_CUDA(c, B.parent.reserve(2 * (size_t)n * 4));
+        HJ_CUDA(c, B.rfirst.reserve((size_t)n * 4)); HJ_CUDA(c, B.rlast.reserve((size_t)n * 4));
+        k_morton<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.bounds.as<int>(), B.keys.as<uint64_t>(), B.vals.as<uint32_t>());
+        uint64_t *k0 = B.keys.as<uint64_t>(), *k1 = B.keys_alt.as<uint64_t>();
+        uint32_t *v0 = B.vals.as<uint32_t>(), *v1 = B.vals_alt.as<uint32_t>();
+        for (int pass = 0; pass < 8; pass++) {      // 63-bit keys: 8 passes of 8 bits, result back in k0/v0
+            k_rs_hist<<<nb, RS_THREADS, 0, st>>>(k0, n, 8 * pass, B.block_hist.as<uint32_t>(), nb);
+            k_rs_scan<<<1, 1024, 0, st>>>(B.block_hist.as<uint32_t>(), 256 * nb);
+            k_rs_scatter<<<nb, RS_THREADS, 0, st>>>(k0, v0, n, 8 * pass, B.block_hist.as<uint32_t>(), nb, k1, v1);
+            std::swap(k0, k1); std::swap(v0, v1);
+        }
+        if (n > 1)
+            k_karras<<<cdiv(n - 1, 256), 256, 0, st>>>(B.keys.as<uint64_t>(), (int)n, B.left.as<uint32_t>(), B.right.as<uint32_t>(),
+                                                       B.parent.as<uint32_t>(), B.rfirst.as<uint32_t>(), B.rlast.as<uint32_t>());
+        B.have_topology = true;
+    }
+    HJ_CUDA(c, B.blo.reserve(2 * (size_t)n * sizeof(float4))); HJ_CUDA(c, B.bhi.reserve(2 * (size_t)n * sizeof(float4)));
+    HJ_CUDA(c, B.flags.reserve((size_t)n * 4));
+    HJ_CUDA(c, cudaMemsetAsync(B.flags.p, 0, (size_t)n * 4, st));
+    k_fit<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.vals.as<uint32_t>(), (int)n, B.left.as<uint32_t>(), B.right.as<uint32_t>(), B.parent.as<uint32_t>(),
+                                        B.flags.as<uint32_t>(), B.blo.as<float4>(), B.bhi.as<float4>());
+    // collapse, level by level
+    HJ_CUDA(c, B.nodes.reserve((size_t)n * 80)); HJ_CUDA(c, B.btris.reserve(3 * (size_t)n * sizeof(float4)));
+    HJ_CUDA(c, B.queue_a.reserve((size_t)n * sizeof(uint2))); HJ_CUDA(c, B.queue_b.reserve((size_t)n * sizeof(uint2)));
+    HJ_CUDA(c, B.counters.reserve(4 * sizeof(uint32_t)));
+    const uint32_t init_counters[4] = {1u, 0u, 0u, 0u};
+    const uint2 root = make_uint2(0u, 0u);
+    HJ_CUDA(c, cudaMemcpyAsync(B.counters.p, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, st));
+    HJ_CUDA(c, cudaMemcpyAsync(B.queue_a.p, &root, sizeof root, cudaMemcpyHostToDevice, st));
+    CollapseArgs a;
+    a.n = (int)n; a.leaf_max = (uint32_t)c->opt_leaf_max;
+    a.left = B.left.as<uint32_t>(); a.right = B.right.as<uint32_t>(); a.rfirst = B.rfirst.as<uint32_t>(); a.rlast = B.rlast.as<uint32_t>();
+    a.sorted = B.vals.as<uint32_t>(); a.blo = B.blo.as<float4>(); a.bhi = B.bhi.as<float4>(); a.tri_pos = c->S.tri_pos;
+    a.nodes = B.nodes.as<uint4>(); a.btris = B.btris.as<float4>(); a.counters = B.counters.as<uint32_t>();
+    uint2 *qi = B.queue_a.as<uint2>(), *qo = B.queue_b.as<uint2>();
+    uint32_t n_in = 1, depth = 0, cnt[4];
+    while (n_in) {
+        HJ_CUDA(c, cudaMemsetAsync(a.counters + 2, 0, 4, st));
+        k_collapse<<<cdiv(n_in, 128), 128, 0, st>>>(a, qi, n_in, qo);
+        HJ_CUDA(c, cudaMemcpyAsync(cnt, a.counters, sizeof cnt, cudaMemcpyDeviceToHost, st));
+        HJ_CUDA(c, cudaStreamSynchronize(st));
+        n_in = cnt[2]; std::swap(qi, qo); depth++;
+        if (depth > 4096) { c->err = "hj_accel_build: collapse did not terminate"; return HJ_ERR_INVALID; }
+    }
+    HJ_CUDA(c, cudaEventRecord(c->ev1, st));
+    HJ_CUDA(c, cudaEventSynchronize(c->ev1));
+    HJ_CUDA(c, cudaGetLastError());
+    float ms = 0; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    if (cnt[1] != n) { c->err = "hj_accel_build: internal error, leaf triangles != scene triangles"; return HJ_ERR_INVALID; }
+    if (depth > HJ_STACK) {
+        char b[160]; snprintf(b, sizeof b, "hj_accel_build: wide BVH depth %u exceeds the traversal stack (%d)", depth, HJ_STACK);
+        c->err = b; return HJ_ERR_INVALID;
+    }
+    B.n_nodes = cnt[0]; B.depth = depth;
+    c->S.nodes = B.nodes.as<uint4>(); c->S.btris = B.btris.as<float4>();
+    c->stats.ms_accel = ms; c->stats.bvh_nodes = B.n_nodes; c->stats.bvh_node_bytes = 80;
+    return HJ_OK;
+}

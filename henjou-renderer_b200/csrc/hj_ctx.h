@@ -1,0 +1,93 @@
+// hj_ctx.h — the context behind the C ABI of include/henjou_b200.h: owns one CUDA stream and every device
+// allocation (the role of Renderer's cuh::CUDevicePointer members, /root/reference/include/cu/cuda_buffer.h:18-98
+// and include/renderer/renderer.h:138-196).
+#pragma once
+#include "../../include/henjou_b200.h"
+#include "hj_scene.cuh"
+#include <string>
+#include <vector>
+#include <cstdio>
+
+struct DevBuf {
+    void* p = nullptr; size_t cap = 0;
+    // grow-only; contents are NOT preserved
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return (T*)p; }
+};
+
+struct BvhState {
+    // binary LBVH (Karras 2012), N leaves = triangles in Morton order
+    DevBuf keys, keys_alt, vals, vals_alt, block_hist;
+    DevBuf blo, bhi;              // float4[2N-1] boxes: internal i -> i, leaf j -> N-1+j
+    DevBuf left, right, parent;   // uint32
+    DevBuf rfirst, rlast, flags;  // uint32[N-1]
+    DevBuf bounds;                // 6 ordered-int atomics
+    DevBuf queue_a, queue_b, counters;   // collapse work queues: uint2 {binary node, wide node}
+    DevBuf nodes, btris;          // the traversal structure
+    uint32_t n_nodes = 0, depth = 0;
+    bool have_topology = false;
+};
+
+struct WavefrontState {
+    uint32_t capacity = 0;        // path slots
+    DevBuf ray_o, ray_d, hit, thr, L, rng_depth, dbg;   // per-slot state (SoA)
+    DevBuf q_extend[2], q_shadow, q_mis;                 // queues
+    DevBuf sh_o, sh_d, sh_c;      // shadow ray payload per slot: origin+tmax, dir, contribution
+    DevBuf mi_o, mi_d, mi_a, mi_t;   // MIS ray payload per slot
+    DevBuf counters;              // device-side queue counters + ray statistics
+};
+
+struct NcclApi;
+
+struct hj_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    // options
+    int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3;
+    int64_t opt_paths_per_pass = 0;
+    // scene
+    bool have_scene = false, have_accel = false, have_frame = false;
+    DevScene S{};                 // device pointers (host copy of the struct, passed to kernels by value)
+    DevBuf d_vertices, d_normals, d_texcoords, d_indices, d_material_ids, d_prim_offsets, d_tri_inst;
+    DevBuf d_xf, d_inv_xf, d_materials, d_textures, d_texels, d_srgb, d_light_ids, d_light_em, d_ibl, d_lut;
+    DevBuf d_tri_pos, d_tri_attr;
+    BvhState bvh;
+    WavefrontState wf;
+    // frame
+    hj_frame_params fp{};
+    DevBuf aov_color, aov_albedo, aov_normal, aov_rgba8, aov_accum, aov_path_rad, aov_path_ids;
+    uint32_t fb_w = 0, fb_h = 0;
+    hj_stats stats{};
+    // multi-GPU
+    NcclApi* nccl = nullptr; void* comm = nullptr; int rank = 0, nranks = 1;
+};
+
+#define HJ_CUDA(ctx, call)                                                                         \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            char b_[512];                                                                          \
+            snprintf(b_, sizeof b_, "%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            (ctx)->err = b_;                                                                       \
+            return (e_ == cudaErrorMemoryAllocation) ? HJ_ERR_OOM : HJ_ERR_CUDA;                   \
+        }                                                                                          \
+    } while (0)
+
+// hj_bvh.cu
+int hj_bvh_build(hj_ctx* c, int mode);
+// hj_wavefront.cu
+int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp);
+int hj_wavefront_finalize(hj_ctx* c);
+int hj_wavefront_stats(hj_ctx* c);
+int hj_trace_batch(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, uint32_t* prim_host, float* tuv_host);

@@ -1,0 +1,504 @@
+// hj_wavefront.cu — wavefront path integrator: the B200 replacement for the reference's megakernel
+// (__raygen__rg + __closesthit__ch + __miss__ms + __closesthit__shadow launched by optixLaunch(W,H,1),
+// /root/reference/include/renderer/renderer.h:1241) and its integrators Pathtrace / NEE / MIS
+// (include/kernel/rt.h:85-159, 162-281, 284-440).
+//
+// One path per slot; slot = s_local * W*H + pixel, so the RNG stream of a path is CMJState{n_spp = global sample
+// index, scramble = frame, image_idx = pixel} regardless of how samples are sliced over passes or GPUs.
+// Per bounce:   k_extend (closest hit)  ->  k_shade (surface, NEE sample, MIS sample, continuation, Russian
+// roulette; pushes shadow / MIS / next-bounce queues with warp-aggregated atomics)  ->  k_shadow (any hit)  ->
+// k_mis (closest hit + emitter evaluation). Queue lengths live in device memory and every kernel is a
+// grid-stride loop over its queue, so a frame is enqueued without a single host synchronisation.
+// The draw order of every RNG dimension and the order of the float additions into the radiance follow the
+// reference loop exactly; rays whose contribution is exactly zero are not traced (they cannot change the result).
+#include "hj_ctx.h"
+#include "hj_bsdf.cuh"
+#include "hj_trace.cuh"
+
+struct WfCounters {
+    uint32_t n_extend[2]; uint32_t n_shadow, n_mis;
+    unsigned long long rays_extend, rays_shadow, nodes, tris;
+};
+
+struct FrameK {
+    uint32_t W, H, WH, spp, frame, sample_begin;
+    float3 cpos, cdir, cup, cright; float cf, ibl;
+    int integrator, max_depth, tonemap, jitter, debug;
+};
+
+struct WfPtrs {
+    float4 *ray_o, *ray_d, *hit, *thr, *L; uint32_t* rng; uint2* dbg;
+    uint32_t *q_ext[2], *q_shadow, *q_mis;
+    float4 *sh_o, *sh_d, *sh_c, *mi_o, *mi_d, *mi_a, *mi_t;
+    WfCounters* cnt;
+    float4 *aov_albedo, *aov_normal;
+};
+
+#define WF_THREADS 128
+
+// warp-aggregated queue push: one atomic per warp; must be reached by all 32 lanes
+HJ_DI void queue_push(uint32_t* counter, uint32_t* queue, bool pred, uint32_t value) {
+    const uint32_t m = __ballot_sync(0xffffffffu, pred);
+    if (!m) return;
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t base = 0;
+    if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+    if (pred) queue[base + __popc(m & ((1u << lane) - 1u))] = value;
+}
+HJ_DI void warp_add64(unsigned long long* p, uint32_t v) {
+    v = __reduce_add_sync(0xffffffffu, v);
+    if ((threadIdx.x & 31u) == 0 && v) atomicAdd(p, (unsigned long long)v);
+}
+
+// the Russian-roulette step that opens every loop iteration (rt.h:96-102 / 173-179 / 295-301)
+HJ_DI bool roulette(float3& thr, Sampler& st) {
+    const float rp = fmaxf(thr.x, fmaxf(thr.y, thr.z));
+    if (rp < draw1(st)) return false;
+    thr /= rp;
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------- raygen
+// Reconstructed __raygen__rg: camera model of the stale PTX computeCameraRay
+// (lib/ptx/HenjouRenderer_generated_henjouRendererCU.cu.ptx:49-104): u = (2x-W)/H, v = (2y-H)/H,
+// d = normalize(camera_f*dir + u*right + v*up); D1: the first CMJ draw of a sample jitters the pixel.
+__global__ void __launch_bounds__(WF_THREADS) k_raygen(FrameK F, WfPtrs P, uint32_t s0, uint32_t n_slots) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_slots; slot += stride) {
+        const uint32_t pix = slot % F.WH, s = s0 + slot / F.WH;
+        const uint32_t x = pix % F.W, y = pix / F.W;
+        Sampler st; st.n_spp = s; st.scramble = F.frame; st.depth = 0; st.image_idx = pix;
+        float jx = 0.0f, jy = 0.0f;
+        if (F.jitter) { const float2 xi = draw2(st); jx = xi.x; jy = xi.y; }
+        const float u = (2.0f * ((float)x + jx) - (float)F.W) / (float)F.H;
+        const float v = (2.0f * ((float)y + jy) - (float)F.H) / (float)F.H;
+        const float3 d = normalize(F.cf * F.cdir + u * F.cright + v * F.cup);
+        float3 thr = f3(1.0f);
+        const bool alive = F.max_depth > 0 && roulette(thr, st);
+        P.ray_o[slot] = f4(F.cpos, 0.0f); P.ray_d[slot] = f4(d, 0.0f);
+        P.thr[slot] = f4(thr, 0.0f); P.L[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        P.rng[slot] = st.depth;
+        if (F.debug) P.dbg[slot] = make_uint2(0xffffffffu, 0x811c9dc5u);
+        if (s == 0) { P.aov_albedo[pix] = make_float4(0, 0, 0, 1); P.aov_normal[pix] = make_float4(0, 0, 0, 1); }
+        // every first-iteration roulette passes (throughput 1 > any draw), so the queue is the identity
+        P.q_ext[0][slot] = alive ? slot : 0xffffffffu;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- extend
+template <bool COUNT>
+__global__ void __launch_bounds__(WF_THREADS) k_extend(DevScene S, FrameK F, WfPtrs P, int cur) {
+    const uint32_t n = P.cnt->n_extend[cur];
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t nn = 0, nt = 0, nr = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint32_t slot = P.q_ext[cur][i];
+        if (slot == 0xffffffffu) continue;
+        const float4 o = P.ray_o[slot], d = P.ray_d[slot];
+        const Hit h = traverse<false, COUNT>(S, f3(o), f3(d), 0.001f, 1e16f, nn, nt);
+        P.hit[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.prim));
+        nr++;
+        if (F.debug) {
+            uint2 g = P.dbg[slot];
+            if (P.L[slot].w == 0.0f) g.x = h.prim;     // first ray of the path
+            g.y = (g.y ^ (h.prim + 1u)) * 0x01000193u;
+            P.dbg[slot] = g;
+        }
+        P.L[slot].w += 1.0f;
+    }
+    warp_add64(&P.cnt->rays_extend, nr);
+    if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
+}
+
+// ---------------------------------------------------------------------------------------------- light sampling
+// light_sample.h:9-75: uniform emissive triangle, binary search of the owning instance, uniform barycentrics,
+// world-space area pdf. Two RNG calls; none when the scene has no emissive triangle (:12-16).
+HJ_DI float3 sample_light(const DevScene& S, Sampler& st, float& pdf, float3& normal, float3& emission) {
+    const int count = (int)S.n_lights;
+    float p = draw1(st);
+    int index = (int)(p * count);
+    if (index == count) index--;
+    const unsigned int prim = S.light_prim_ids[index];
+    unsigned int left = 0U, right = S.n_instances - 1, middle = (left + right) / 2U;
+    while (left <= right) {
+        if (S.prim_offsets[middle] <= prim) left = middle + 1;
+        else { if (middle == 0) { break; } right = middle - 1; }
+        middle = (left + right) / 2;
+    }
+    const float select_pdf = 1.0f / count;
+    const unsigned int inst = middle;
+    const float4* xf = S.xf + 3 * (size_t)inst; const float4* ixf = S.inv_xf + 3 * (size_t)inst;
+    const unsigned i0 = S.indices[prim * 3 + 0], i1 = S.indices[prim * 3 + 1], i2 = S.indices[prim * 3 + 2];
+    const float3 v0 = xform_point(xf, ld3(S.vertices, i0)), v1 = xform_point(xf, ld3(S.vertices, i1)), v2 = xform_point(xf, ld3(S.vertices, i2));
+    const float3 n0 = xform_normal(ixf, ld3(S.normals, i0)), n1 = xform_normal(ixf, ld3(S.normals, i1)), n2 = xform_normal(ixf, ld3(S.normals, i2));
+    const float area = length(cross(v1 - v0, v2 - v0)) * 0.5f;
+    const float2 xi = draw2(st);
+    const float f1 = 1.0f - sqrtf(xi.x);
+    const float f2 = sqrtf(xi.x) * (1.0f - xi.y);
+    const float f3_ = sqrtf(xi.x) * xi.y;
+    const float3 pos = v0 * f1 + v1 * f2 + v2 * f3_;
+    const float3 nrm = normalize(n0 * f1 + n1 * f2 + n2 * f3_);
+    pdf = 1.0 / area;           // double division, rounded to float (light_sample.h:69)
+    pdf *= select_pdf;
+    normal = nrm;
+    emission = ld3(S.light_prim_emission, (uint32_t)index);
+    return pos;
+}
+// light_sample.h:77-92 (the world-space vertices are the flattened ones: same transform_position results)
+HJ_DI float light_pdf_area(const DevScene& S, uint32_t prim) {
+    const float4* P = S.tri_pos + 3 * (size_t)prim;
+    const float3 v0 = f3(P[0]), v1 = f3(P[1]), v2 = f3(P[2]);
+    const float area = length(cross(v1 - v0, v2 - v0)) * 0.5f;
+    return 1.0f / (area * (int)S.n_lights);
+}
+
+// ---------------------------------------------------------------------------------------------- shade
+// One loop iteration of Pathtrace / NEE / MIS after the closest-hit query (rt.h:104-156 / 181-278 / 303-438),
+// followed by the Russian roulette that opens the NEXT iteration. INTEG: hj_integrator.
+template <int INTEG>
+__global__ void __launch_bounds__(WF_THREADS) k_shade(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
+    const uint32_t n = P.cnt->n_extend[cur];
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
+        const uint32_t slot = (i < n) ? P.q_ext[cur][i] : 0xffffffffu;
+        bool push_shadow = false, push_mis = false, push_next = false;
+        if (slot != 0xffffffffu) {
+            const float4 hq = P.hit[slot];
+            const uint32_t prim = __float_as_uint(hq.w);
+            const float3 d = f3(P.ray_d[slot]);
+            float3 thr = f3(P.thr[slot]);
+            const float4 Lq = P.L[slot];
+            float3 L = f3(Lq);
+            const uint32_t pix = slot % F.WH;
+            Sampler st; st.n_spp = s0 + slot / F.WH; st.scramble = F.frame; st.image_idx = pix; st.depth = P.rng[slot];
+            const bool first_sample = (depth == 0 && st.n_spp == 0);
+            if (prim == 0xffffffffu) {                               // __miss__ms (D6); AOVs stay 0 (raygen wrote them)
+                const float3 em = sky_radiance(S, d, F.ibl);
+                if (INTEG == HJ_INTEGRATOR_PT || depth == 0) { L += thr * em; P.L[slot] = f4(L, Lq.w); }
+            } else {
+                const Surface prd = make_surface(S, prim, hq.y, hq.z);
+                if (first_sample) { P.aov_albedo[pix] = f4(prd.basecolor, 1.0f); P.aov_normal[pix] = f4(prd.normal, 1.0f); }   // rt.h:113-116
+                if (prd.is_light) {
+                    if (INTEG == HJ_INTEGRATOR_PT || depth == 0) { L += thr * prd.emission; P.L[slot] = f4(L, Lq.w); }
+                } else {
+                    SurfaceBsdf bsdf; bsdf.init(prd);
+                    float3 t, b; const float3 nrm = prd.normal;
+                    onb(nrm, t, b);
+                    const float3 lwo = to_local(-d, t, nrm, b);
+                    if (INTEG != HJ_INTEGRATOR_PT && S.n_lights >= 1) {          // light sampling, rt.h:219-260 / 341-380
+                        float lpdf; float3 lnrm, lem;
+                        const float3 lpos = sample_light(S, st, lpdf, lnrm, lem);
+                        float3 ld = lpos - prd.position;
+                        const float dist = length(ld);
+                        ld = normalize(ld);
+                        const float c1 = absdot(nrm, ld), c2 = absdot(lnrm, -ld);
+                        const float3 lwi = to_local(ld, t, nrm, b);
+                        const float3 f = bsdf.eval(S, lwo, lwi);
+                        const float G = c2 / (dist * dist);
+                        float3 contrib;
+                        if (INTEG == HJ_INTEGRATOR_MIS) {
+                            const float ppdf = bsdf.pdf(lwo, lwi) * G;
+                            const float w = lpdf / (lpdf + ppdf);
+                            contrib = thr * (f * G * c1 / lpdf) * w * lem;
+                        } else contrib = thr * (f * G * c1 / lpdf) * lem;
+                        if (!is_zero3(contrib)) {
+                            push_shadow = true;
+                            P.sh_o[slot] = f4(prd.position, dist - 0.001f); P.sh_d[slot] = f4(ld, 0.0f); P.sh_c[slot] = f4(contrib, 0.0f);
+                        }
+                    }
+                    if (INTEG == HJ_INTEGRATOR_MIS) {                            // BSDF sampling towards emitters, rt.h:383-420
+                        float ppdf = 1.0f;                  // defined (reference: uninitialised)
+                        float3 lwi = f3(0.0f, 1.0f, 0.0f);  // defined (reference: uninitialised)
+                        const float3 f = bsdf.sample(S, lwo, lwi, ppdf, st);
+                        const float3 wi = to_world(lwi, t, nrm, b);
+                        const float c1 = absdot(wi, nrm);
+                        if (!is_zero3(f * c1)) {
+                            push_mis = true;
+                            P.mi_o[slot] = f4(prd.position, c1); P.mi_d[slot] = f4(wi, ppdf);
+                            P.mi_a[slot] = f4(f, prd.is_specular ? 1.0f : 0.0f); P.mi_t[slot] = f4(thr, 0.0f);
+                        }
+                    }
+                    if (INTEG != HJ_INTEGRATOR_PT) (void)draw2(st);              // dead draw, rt.h:266 / 426
+                    float pdf = 1.0f;
+                    float3 lwi = f3(0.0f, 1.0f, 0.0f);
+                    const float3 f = bsdf.sample(S, lwo, lwi, pdf, st);          // continuation, rt.h:141 / 269 / 429
+                    const float3 wi = to_world(lwi, t, nrm, b);
+                    thr *= f * fabsf(dot(wi, nrm)) / pdf;
+                    if (depth + 1 < F.max_depth && roulette(thr, st)) {          // opens iteration depth+1
+                        push_next = true;
+                        P.ray_o[slot] = f4(prd.position, 0.0f); P.ray_d[slot] = f4(wi, 0.0f);
+                        P.thr[slot] = f4(thr, 0.0f); P.rng[slot] = st.depth;
+                    }
+                }
+            }
+        }
+        queue_push(&P.cnt->n_shadow, P.q_shadow, push_shadow, slot);
+        queue_push(&P.cnt->n_mis, P.q_mis, push_mis, slot);
+        queue_push(&P.cnt->n_extend[cur ^ 1], P.q_ext[cur ^ 1], push_next, slot);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- shadow / MIS rays
+// TraceOcculution (rt.h:15-41): any hit in (1e-3, dist-1e-3) discards the light sample.
+template <bool COUNT>
+__global__ void __launch_bounds__(WF_THREADS) k_shadow(DevScene S, WfPtrs P) {
+    const uint32_t n = P.cnt->n_shadow;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t nn = 0, nt = 0, nr = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint32_t slot = P.q_shadow[i];
+        const float4 o = P.sh_o[slot], d = P.sh_d[slot];
+        const Hit h = traverse<true, COUNT>(S, f3(o), f3(d), 0.001f, o.w, nn, nt);
+        float4 L = P.L[slot];
+        if (h.prim == 0xffffffffu) { const float4 c = P.sh_c[slot]; L.x += c.x; L.y += c.y; L.z += c.z; }
+        L.w += 1.0f;
+        P.L[slot] = L;
+        nr++;
+    }
+    warp_add64(&P.cnt->rays_shadow, nr);
+    if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
+}
+
+// The extra BSDF-sampled ray of MIS (rt.h:383-420): emitter hit weighted by the balance heuristic, sky unweighted.
+template <bool COUNT>
+__global__ void __launch_bounds__(WF_THREADS) k_mis(DevScene S, FrameK F, WfPtrs P) {
+    const uint32_t n = P.cnt->n_mis;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t nn = 0, nt = 0, nr = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint32_t slot = P.q_mis[i];
+        const float4 oq = P.mi_o[slot], dq = P.mi_d[slot], aq = P.mi_a[slot];
+        const float3 org = f3(oq), wi = f3(dq), f = f3(aq), thr = f3(P.mi_t[slot]);
+        const float c1 = oq.w, ppdf = dq.w;
+        const Hit h = traverse<false, COUNT>(S, org, wi, 0.001f, 1e16f, nn, nt);
+        float4 Lq = P.L[slot];
+        float3 L = f3(Lq);
+        if (h.prim != 0xffffffffu) {
+            const float4 a3 = S.tri_attr[4 * (size_t)h.prim + 3];
+            const DevMaterial& m = S.materials[__float_as_uint(a3.w)];
+            if (m.is_light) {
+                const float4* Pp = S.tri_pos + 3 * (size_t)h.prim; const float4* A = S.tri_attr + 4 * (size_t)h.prim;
+                const float b0 = 1.0f - h.b1 - h.b2;
+                const float3 pos = b0 * f3(Pp[0]) + h.b1 * f3(Pp[1]) + h.b2 * f3(Pp[2]);
+                const float3 ln = normalize(b0 * f3(A[0]) + h.b1 * f3(A[1]) + h.b2 * f3(A[2]));
+                const float3 em = f3(m.emission[0], m.emission[1], m.emission[2]);
+                const float c2 = absdot(-wi, ln);
+                const float dist = length(pos - org);
+                const float invG = dist * dist / c2;
+                const float lpdf = (aq.w != 0.0f) ? 0.0f : light_pdf_area(S, h.prim) * invG;
+                const float w = ppdf / (ppdf + lpdf);
+                L += thr * w * c1 * em * f / ppdf;
+            }
+        } else {
+            const float3 em = sky_radiance(S, wi, F.ibl);
+            L += thr * f * c1 * em / ppdf;
+        }
+        if (F.debug) { uint2 g = P.dbg[slot]; g.y = (g.y ^ (h.prim + 1u)) * 0x01000193u; P.dbg[slot] = g; }
+        P.L[slot] = f4(L, Lq.w + 1.0f);
+        nr++;
+    }
+    warp_add64(&P.cnt->rays_extend, nr);
+    if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
+}
+
+// ---------------------------------------------------------------------------------------------- accumulate / write-out
+__global__ void k_reset_queues(WfCounters* c, uint32_t n0, int all) {
+    if (all) { c->n_extend[0] = n0; c->n_extend[1] = 0; }
+    c->n_shadow = 0; c->n_mis = 0;
+}
+__global__ void k_swap_queues(WfCounters* c, int cur) { c->n_extend[cur] = 0; c->n_shadow = 0; c->n_mis = 0; }
+
+// end of a pass: per pixel, add the pass's samples in sample order (same float addition order as the
+// reference's spp loop), and export the per-path debug records
+__global__ void k_accumulate(FrameK F, WfPtrs P, float4* accum, uint32_t s0, uint32_t n_samples, float4* path_rad, uint2* path_ids) {
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= F.WH) return;
+    float4 a = accum[pix];
+    for (uint32_t s = 0; s < n_samples; s++) {
+        const size_t slot = (size_t)s * F.WH + pix;
+        const float4 L = P.L[slot];
+        a.x += L.x; a.y += L.y; a.z += L.z; a.w += 1.0f;
+        if (F.debug) {
+            const size_t o = (size_t)(s0 + s - F.sample_begin) * F.WH + pix;
+            path_rad[o] = L; path_ids[o] = P.dbg[slot];
+        }
+    }
+    accum[pix] = a;
+}
+
+// mean -> tonemap (kernel/color.h) -> float4 colour AOV; RGBA8 = float4ConvertColor (renderer.h:87-101)
+__global__ void k_finalize(FrameK F, const float4* accum, float4* color, uchar4* rgba8) {
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= F.WH) return;
+    const float4 a = accum[pix];
+    const float inv = 1.0f / (float)F.spp;
+    float3 col = f3(a) * inv;
+    if (F.tonemap == HJ_TONEMAP_ACES) col = tonemap_aces(col);
+    else if (F.tonemap == HJ_TONEMAP_UCHIMURA) col = tonemap_uchimura(col);
+    color[pix] = f4(col, 1.0f);
+    const float3 sc = to_srgb(col);
+    rgba8[pix] = make_uchar4(quantize8(sc.x), quantize8(sc.y), quantize8(sc.z), 255);
+}
+
+// ---------------------------------------------------------------------------------------------- batch trace (hj_trace)
+template <bool ANY>
+__global__ void __launch_bounds__(WF_THREADS) k_trace_batch(DevScene S, const float4* rays, uint64_t n, uint32_t* prim, float* tuv) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 o = rays[2 * i], d = rays[2 * i + 1];
+    uint32_t nn = 0, nt = 0;
+    const Hit h = traverse<ANY, false>(S, f3(o), f3(d), o.w, d.w, nn, nt);
+    const bool hit = h.prim != 0xffffffffu;
+    if (ANY) prim[i] = hit ? 1u : 0xffffffffu;
+    else {
+        prim[i] = h.prim;
+        tuv[3 * i] = hit ? h.t : 0.0f; tuv[3 * i + 1] = hit ? h.b1 : 0.0f; tuv[3 * i + 2] = hit ? h.b2 : 0.0f;
+    }
+}
+
+int hj_trace_batch(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, uint32_t* prim_host, float* tuv_host) {
+    if (n == 0) return HJ_OK;
+    DevBuf dr, dp, dt;
+    HJ_CUDA(c, dr.reserve(n * 32)); HJ_CUDA(c, dp.reserve(n * 4)); HJ_CUDA(c, dt.reserve(n * 12));
+    HJ_CUDA(c, cudaMemcpyAsync(dr.p, rays_host, n * 32, cudaMemcpyHostToDevice, c->stream));
+    const uint32_t grid = (uint32_t)((n + WF_THREADS - 1) / WF_THREADS);
+    if (any_hit) k_trace_batch<true><<<grid, WF_THREADS, 0, c->stream>>>(c->S, dr.as<float4>(), n, dp.as<uint32_t>(), dt.as<float>());
+    else k_trace_batch<false><<<grid, WF_THREADS, 0, c->stream>>>(c->S, dr.as<float4>(), n, dp.as<uint32_t>(), dt.as<float>());
+    if (prim_host) HJ_CUDA(c, cudaMemcpyAsync(prim_host, dp.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (tuv_host && !any_hit) HJ_CUDA(c, cudaMemcpyAsync(tuv_host, dt.p, n * 12, cudaMemcpyDeviceToHost, c->stream));
+    HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    HJ_CUDA(c, cudaGetLastError());
+    dr.release(); dp.release(); dt.release();
+    return HJ_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- host driver
+static inline uint32_t cdiv_u(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
+
+static int wf_reserve(hj_ctx* c, uint32_t cap, bool mis, bool debug) {
+    WavefrontState& w = c->wf;
+    const size_t f4s = (size_t)cap * sizeof(float4);
+    HJ_CUDA(c, w.ray_o.reserve(f4s)); HJ_CUDA(c, w.ray_d.reserve(f4s)); HJ_CUDA(c, w.hit.reserve(f4s));
+    HJ_CUDA(c, w.thr.reserve(f4s)); HJ_CUDA(c, w.L.reserve(f4s)); HJ_CUDA(c, w.rng_depth.reserve((size_t)cap * 4));
+    HJ_CUDA(c, w.dbg.reserve(debug ? (size_t)cap * 8 : 8));
+    HJ_CUDA(c, w.q_extend[0].reserve((size_t)cap * 4)); HJ_CUDA(c, w.q_extend[1].reserve((size_t)cap * 4));
+    HJ_CUDA(c, w.q_shadow.reserve((size_t)cap * 4)); HJ_CUDA(c, w.q_mis.reserve((size_t)cap * 4));
+    HJ_CUDA(c, w.sh_o.reserve(f4s)); HJ_CUDA(c, w.sh_d.reserve(f4s)); HJ_CUDA(c, w.sh_c.reserve(f4s));
+    if (mis) { HJ_CUDA(c, w.mi_o.reserve(f4s)); HJ_CUDA(c, w.mi_d.reserve(f4s)); HJ_CUDA(c, w.mi_a.reserve(f4s)); HJ_CUDA(c, w.mi_t.reserve(f4s)); }
+    HJ_CUDA(c, w.counters.reserve(sizeof(WfCounters)));
+    w.capacity = cap;
+    return HJ_OK;
+}
+
+int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
+    const uint32_t W = fp->width, H = fp->height;
+    const uint64_t WH = (uint64_t)W * H;
+    if (W == 0 || H == 0 || fp->spp == 0 || fp->sample_end < fp->sample_begin || fp->max_depth < 0 || WH > 0x7fffffffull) {
+        c->err = "hj_render: invalid frame parameters"; return HJ_ERR_INVALID;
+    }
+    if (fp->integrator < HJ_INTEGRATOR_PT || fp->integrator > HJ_INTEGRATOR_MIS) { c->err = "hj_render: unknown integrator"; return HJ_ERR_INVALID; }
+    const uint32_t ns = fp->sample_end - fp->sample_begin;
+    const bool debug = fp->debug_paths != 0;
+    // path slots per pass: whole samples of the whole frame
+    uint64_t target = c->opt_paths_per_pass > 0 ? (uint64_t)c->opt_paths_per_pass : (4ull << 20);
+    uint32_t spass = (uint32_t)(target / WH); if (spass < 1) spass = 1; if (spass > ns && ns) spass = ns;
+    if (spass * WH > 0xfffffff0ull) spass = (uint32_t)(0xfffffff0ull / WH);
+    const uint32_t cap = (uint32_t)(spass * WH);
+    int rc = wf_reserve(c, cap, fp->integrator == HJ_INTEGRATOR_MIS, debug); if (rc) return rc;
+    const size_t fb = (size_t)WH * sizeof(float4);
+    HJ_CUDA(c, c->aov_color.reserve(fb)); HJ_CUDA(c, c->aov_albedo.reserve(fb)); HJ_CUDA(c, c->aov_normal.reserve(fb));
+    HJ_CUDA(c, c->aov_accum.reserve(fb)); HJ_CUDA(c, c->aov_rgba8.reserve((size_t)WH * 4));
+    if (debug) { HJ_CUDA(c, c->aov_path_rad.reserve((size_t)ns * fb)); HJ_CUDA(c, c->aov_path_ids.reserve((size_t)ns * WH * 8)); }
+    cudaStream_t st = c->stream;
+    if (c->fb_w != W || c->fb_h != H) {
+        HJ_CUDA(c, cudaMemsetAsync(c->aov_albedo.p, 0, fb, st)); HJ_CUDA(c, cudaMemsetAsync(c->aov_normal.p, 0, fb, st));
+        c->fb_w = W; c->fb_h = H;
+    }
+    FrameK F;
+    F.W = W; F.H = H; F.WH = (uint32_t)WH; F.spp = fp->spp; F.frame = fp->frame; F.sample_begin = fp->sample_begin;
+    F.cpos = make_float3(fp->camera_pos[0], fp->camera_pos[1], fp->camera_pos[2]);
+    F.cdir = make_float3(fp->camera_dir[0], fp->camera_dir[1], fp->camera_dir[2]);
+    F.cup = make_float3(fp->camera_up[0], fp->camera_up[1], fp->camera_up[2]);
+    F.cright = make_float3(fp->camera_right[0], fp->camera_right[1], fp->camera_right[2]);
+    F.cf = fp->camera_f; F.ibl = fp->ibl_intensity;
+    F.integrator = fp->integrator; F.max_depth = fp->max_depth; F.tonemap = fp->tonemap; F.jitter = fp->pixel_jitter; F.debug = debug;
+    WavefrontState& w = c->wf;
+    WfPtrs P;
+    P.ray_o = w.ray_o.as<float4>(); P.ray_d = w.ray_d.as<float4>(); P.hit = w.hit.as<float4>(); P.thr = w.thr.as<float4>();
+    P.L = w.L.as<float4>(); P.rng = w.rng_depth.as<uint32_t>(); P.dbg = w.dbg.as<uint2>();
+    P.q_ext[0] = w.q_extend[0].as<uint32_t>(); P.q_ext[1] = w.q_extend[1].as<uint32_t>();
+    P.q_shadow = w.q_shadow.as<uint32_t>(); P.q_mis = w.q_mis.as<uint32_t>();
+    P.sh_o = w.sh_o.as<float4>(); P.sh_d = w.sh_d.as<float4>(); P.sh_c = w.sh_c.as<float4>();
+    P.mi_o = w.mi_o.as<float4>(); P.mi_d = w.mi_d.as<float4>(); P.mi_a = w.mi_a.as<float4>(); P.mi_t = w.mi_t.as<float4>();
+    P.cnt = w.counters.as<WfCounters>();
+    P.aov_albedo = c->aov_albedo.as<float4>(); P.aov_normal = c->aov_normal.as<float4>();
+
+    int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    const uint32_t grid_cap = (uint32_t)sms * 16u;
+    const uint32_t grid = std::min(cdiv_u(cap, WF_THREADS), grid_cap);
+    const bool count = c->opt_count_fetches != 0;
+    uint64_t launches = 0;
+
+    HJ_CUDA(c, cudaEventRecord(c->ev0, st));
+    HJ_CUDA(c, cudaMemsetAsync(w.counters.p, 0, sizeof(WfCounters), st));
+    HJ_CUDA(c, cudaMemsetAsync(c->aov_accum.p, 0, fb, st));
+    for (uint32_t s0 = fp->sample_begin; s0 < fp->sample_end; s0 += spass) {
+        const uint32_t nsamp = std::min(spass, fp->sample_end - s0);
+        const uint32_t nslots = (uint32_t)(nsamp * WH);
+        k_reset_queues<<<1, 1, 0, st>>>(P.cnt, nslots, 1);
+        k_raygen<<<grid, WF_THREADS, 0, st>>>(F, P, s0, nslots);
+        launches += 2;
+        int cur = 0;
+        for (int depth = 0; depth < fp->max_depth; depth++) {
+            if (count) k_extend<true><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur);
+            else k_extend<false><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur);
+            if (fp->integrator == HJ_INTEGRATOR_PT) k_shade<HJ_INTEGRATOR_PT><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur, depth, s0);
+            else if (fp->integrator == HJ_INTEGRATOR_NEE) k_shade<HJ_INTEGRATOR_NEE><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur, depth, s0);
+            else k_shade<HJ_INTEGRATOR_MIS><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur, depth, s0);
+            launches += 2;
+            if (fp->integrator != HJ_INTEGRATOR_PT) {
+                if (count) k_shadow<true><<<grid, WF_THREADS, 0, st>>>(c->S, P);
+                else k_shadow<false><<<grid, WF_THREADS, 0, st>>>(c->S, P);
+                launches++;
+            }
+            if (fp->integrator == HJ_INTEGRATOR_MIS) {
+                if (count) k_mis<true><<<grid, WF_THREADS, 0, st>>>(c->S, F, P);
+                else k_mis<false><<<grid, WF_THREADS, 0, st>>>(c->S, F, P);
+                launches++;
+            }
+            k_swap_queues<<<1, 1, 0, st>>>(P.cnt, cur);
+            launches++;
+            cur ^= 1;
+        }
+        k_accumulate<<<cdiv_u(WH, 256), 256, 0, st>>>(F, P, c->aov_accum.as<float4>(), s0, nsamp, c->aov_path_rad.as<float4>(), c->aov_path_ids.as<uint2>());
+        launches++;
+    }
+    k_finalize<<<cdiv_u(WH, 256), 256, 0, st>>>(F, c->aov_accum.as<float4>(), c->aov_color.as<float4>(), c->aov_rgba8.as<uchar4>());
+    launches++;
+    HJ_CUDA(c, cudaEventRecord(c->ev1, st));
+    HJ_CUDA(c, cudaGetLastError());
+    c->fp = *fp; c->have_frame = true;
+    c->stats.kernel_launches = launches;
+    c->stats.paths = (uint64_t)ns * WH;
+    return HJ_OK;
+}
+
+int hj_wavefront_finalize(hj_ctx* c) {
+    const hj_frame_params& fp = c->fp;
+    FrameK F{}; F.W = fp.width; F.H = fp.height; F.WH = fp.width * fp.height; F.spp = fp.spp; F.tonemap = fp.tonemap;
+    k_finalize<<<cdiv_u(F.WH, 256), 256, 0, c->stream>>>(F, c->aov_accum.as<float4>(), c->aov_color.as<float4>(), c->aov_rgba8.as<uchar4>());
+    HJ_CUDA(c, cudaGetLastError());
+    return HJ_OK;
+}
+
+// reads the device counters of the last frame into ctx->stats (after the stream has been synchronised)
+int hj_wavefront_stats(hj_ctx* c) {
+    if (!c->wf.counters.p) return HJ_OK;
+    WfCounters h;
+    HJ_CUDA(c, cudaMemcpy(&h, c->wf.counters.p, sizeof h, cudaMemcpyDeviceToHost));
+    c->stats.rays_extend = h.rays_extend; c->stats.rays_shadow = h.rays_shadow;
+    c->stats.nodes_fetched = h.nodes; c->stats.tris_fetched = h.tris;
+    float ms = 0; if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->stats.ms_render = ms;
+    return HJ_OK;
+}

@@ -157,7 +157,7 @@ int hj_create(hj_ctx** out, int device);
 void hj_destroy(hj_ctx* ctx);
 const char* hj_last_error(const hj_ctx* ctx);   /* ctx may be NULL: last hj_create error */
 
-/* "count_fetches" 0|1, "time_stages" 0|1, "paths_per_pass" N (0 = auto), "wide_bvh" 0|1 */
+/* "count_fetches" 0|1, "time_stages" 0|1, "paths_per_pass" N (0 = auto), "leaf_max" 1..4 (triangles per BVH leaf) */
 int hj_set_option(hj_ctx* ctx, const char* key, int64_t value);
 
 /* ≙ Renderer::cpySceneDataToDevice + textureBind + setSky + setLUT (renderer.h:197-255, 740-898). */
@@ -185,6 +185,12 @@ void* hj_device_ptr(hj_ctx* ctx, int aov);
 int hj_finalize(hj_ctx* ctx);
 
 int hj_get_stats(hj_ctx* ctx, hj_stats* out);
+
+/* Batch ray query against the current acceleration structure — the two optixTrace call sites of the reference
+ * (RayTrace rt.h:43-69: closest hit; TraceOcculution rt.h:15-41: any hit) exposed on their own for parity checks.
+ * rays: 8 floats each (ox,oy,oz,tmin, dx,dy,dz,tmax), HOST memory. prim[i] = global primitive id of the closest
+ * hit (ties on t -> lower id) or 0xffffffff; any_hit: 1 / 0xffffffff. tuv: 3 floats per ray (t,b1,b2), may be NULL. */
+int hj_trace(hj_ctx* ctx, const float* rays, uint64_t n, int any_hit, uint32_t* prim, float* tuv);
 
 /* Multi-GPU: sample-slice data parallelism, replicated scene, one sum-reduction of the
  * float4 accumulation buffer per frame over NCCL/NVLink. unique_id is the 128-byte ncclUniqueId. */
