@@ -37,7 +37,7 @@ HJ_DI RayPrep prep_ray(const float3& o, const float3& d) {
     r.idir.x = (ax > 1e-30f) ? 1.0f / d.x : copysignf(1e30f, d.x);
     r.idir.y = (ay > 1e-30f) ? 1.0f / d.y : copysignf(1e30f, d.y);
     r.idir.z = (az > 1e-30f) ? 1.0f / d.z : copysignf(1e30f, d.z);
-    r.oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+    r.oct = (r.idir.x < 0.0f ? 1u : 0u) | (r.idir.y < 0.0f ? 2u : 0u) | (r.idir.z < 0.0f ? 4u : 0u);   // from idir: -0.0 counts as negative
     return r;
 }
 
