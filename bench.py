@@ -1,0 +1,288 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the hot path (BASELINE.json): Mrays/s (and spp/s) of the path tracer at
+1920x1080 on the rtcamp-like scene, 64 spp, thin-film materials on, MIS, max depth 10 (config C2).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c5]
+
+A step = one whole frame (all pixels x all samples of this rank's slice) through the wavefront integrator.
+  value   : whole-job Mrays/s, scene + BVH resident in HBM, device time (CUDA events on the context's stream),
+            max over ranks.
+  e2e     : the same metric through the C ABI with HOST buffers, every step: hj_scene_upload (geometry H2D) +
+            hj_accel_build (transforms H2D, BVH rebuild ≙ updateIASMatrix) + hj_render + hj_readback of the colour
+            AOV and the RGBA8 image (D2H), wall clock.
+  roofline: traversal kernels (k_extend + k_shadow + k_mis): algorithmic bytes = 80 B x nodes fetched + 48 B x
+            triangles fetched (counters-enabled pass) / their summed launch durations (event pairs, separate pass).
+  cpu_baseline: the reference's own device headers compiled for the host (oracle/_ref, kind "reference") or the
+            CPU restatement (kind "port"), all host cores, on a bounded sample (pixel rows x few spp) of the workload.
+N > 1 (torchrun): each rank renders its own slice of 64 global sample indices for every pixel (weak scaling,
+replicated scene), then one NCCL all-reduce of the float4 accumulation buffer per frame, inside the timed region.
+`--impl reference` times the CPU reference arm only (rank 0)."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+
+def make_workload(name):
+    """-> (scene, dict(width,height,spp,max_depth,integrator,frame), description)"""
+    import henjou_renderer_b200 as hj
+    from henjou_renderer_b200 import scenes, abi
+    if name == "c2":
+        s = scenes.rtcamp_like()
+        return s, dict(width=1920, height=1080, spp=64, max_depth=10, integrator=abi.INTEGRATOR_MIS, frame=1), \
+            "C2 rtcamp-like temple+statue (procedural stand-in, seed 9), 1920x1080, 64 spp, thin-film on, MIS, depth 10"
+    if name == "c1":
+        s = hj.load_npz(os.path.join(ROOT, "tests", "golden", "cornelbox.npz"))
+        s.set_sky((0.8, 0.8, 0.8))
+        return s, dict(width=512, height=512, spp=16, max_depth=8, integrator=abi.INTEGRATOR_MIS, frame=1), \
+            "C1 cornelbox.gltf 512x512, 16 spp, MIS, depth 8"
+    if name == "c3":
+        s = scenes.metaglass_room()
+        return s, dict(width=1920, height=1080, spp=16, max_depth=32, integrator=abi.INTEGRATOR_MIS, frame=1), \
+            "C3 metamaterial-glass room 1920x1080, 16 spp, MIS, depth 32"
+    if name == "c5":
+        s = scenes.icosphere_field()
+        return s, dict(width=3840, height=2160, spp=8, max_depth=10, integrator=abi.INTEGRATOR_MIS, frame=1), \
+            "C5 ~10M-triangle icosphere field 3840x2160, 8 spp per step, MIS, depth 10"
+    raise SystemExit("unknown workload " + name)
+
+
+def frame_for(scene, cfg, spp_total, sample_begin, sample_end):
+    import henjou_renderer_b200 as hj
+    return hj.frame_params(scene, cfg["width"], cfg["height"], spp_total, frame=cfg["frame"], max_depth=cfg["max_depth"],
+                           integrator=cfg["integrator"], sample_begin=sample_begin, sample_end=sample_end)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            pass
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm))
+
+
+def cpu_arm(scene, cfg, budget_s=15.0, steps=1, warmup=0):
+    """Times the CPU implementation of the path on a bounded sample of the workload: pixel rows around the image
+    centre x `spp_s` samples, all host threads. Returns (Mrays/s per step list, info)."""
+    import oracle_binding as ob
+    kind = "reference" if (ob.lib("reference") is not None and cfg["max_depth"] == 10) else "restatement"
+    xf, inv = scene.transforms(cfg["frame"] / 24.0)
+    o = ob.Oracle(scene, kind, xforms=xf, inv_xforms=inv)
+    W, H = cfg["width"], cfg["height"]
+    cores = os.cpu_count() or 1
+    spp_s = min(2, cfg["spp"])
+    # probe: 2 rows -> paths/s -> size the sample for ~budget_s
+    y0 = H // 2
+    fp = frame_for(scene, cfg, cfg["spp"], 0, spp_s)
+    t = time.time(); r = o.render(fp, threads=0, rows=(y0, y0 + 2)); dt = max(time.time() - t, 1e-3)
+    rows = int(max(2, min(H // 2, (budget_s / dt) * 2)))
+    rows -= rows % 2
+    y0 = (H - rows) // 2
+    vals, last = [], None
+    for i in range(warmup + steps):
+        r = o.render(fp, threads=0, rows=(y0, y0 + rows))
+        rays = r["rays_extend"] + r["rays_shadow"]
+        if i >= warmup:
+            vals.append(rays / r["seconds"] / 1e6)
+        last = r
+    info = dict(kind="reference" if kind == "reference" else "port", cores=cores,
+                sample="%d pixel rows (y %d..%d) x %d px x %d spp of the workload, %.1f s per step, %d rays" %
+                       (rows, y0, y0 + rows, W, spp_s, last["seconds"], last["rays_extend"] + last["rays_shadow"]),
+                seconds=last["seconds"], rays=int(last["rays_extend"] + last["rays_shadow"]),
+                spp_per_s=rows * W * spp_s / last["seconds"] / (W * H))
+    o.close()
+    return vals, info
+
+
+def gpu_arm(args, rank, world, local_rank):
+    import henjou_renderer_b200 as hj
+    from henjou_renderer_b200 import abi
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    scene, cfg, desc = make_workload(args.workload)
+    W, H, spp = cfg["width"], cfg["height"], cfg["spp"]
+    r = hj.Renderer(local_rank)
+    r.upload(scene)
+    xf, inv = scene.transforms(cfg["frame"] / 24.0)
+    r.build_accel(xf, inv)
+    accel_ms = r.stats()["ms_accel"]
+    # weak scaling: every rank renders `spp` samples; the frame has spp*world global sample indices
+    fp = frame_for(scene, cfg, spp * world, rank * spp, (rank + 1) * spp)
+    if world > 1:
+        import torch
+        uid = [hj.Renderer.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        r.comm_init(uid[0], rank, world)
+
+    def barrier():
+        if world > 1:
+            import torch
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def step():
+        r.render(fp, sync=False)
+        if world > 1:
+            r.comm_reduce()          # NCCL all-reduce of the accumulation buffer + finalize (syncs the stream)
+        r.sync()
+
+    for _ in range(args.warmup):
+        step()
+    clocks = ClockSampler(local_rank)
+    barrier()
+    t0 = time.perf_counter()
+    dev_ms, rays, launches = 0.0, 0, 0
+    for _ in range(args.steps):
+        step()
+        st = r.stats()
+        dev_ms += st["ms_render"]; rays += st["rays_extend"] + st["rays_shadow"]; launches += st["kernel_launches"]
+    barrier()
+    wall = time.perf_counter() - t0
+    clk = clocks.stop()
+    # device time per rank = its render events (+ the all-reduce, covered by wall); take the max over ranks of wall
+    t_rank = wall if world > 1 else dev_ms / 1e3
+    if world > 1:
+        import torch
+        tt = torch.tensor([t_rank, float(rays), float(launches)], dtype=torch.float64, device="cuda")
+        tmax = tt.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = tt.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        t_all, rays_all, launches_all = float(tmax[0]), int(tsum[1]), int(tsum[2])
+    else:
+        t_all, rays_all, launches_all = t_rank, rays, launches
+    value = rays_all / t_all / 1e6
+    out = dict(metric="Mrays/s", value=round(value, 2), unit="Mrays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
+               ms_per_step=round(1e3 * t_all / args.steps, 3), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
+               data="synthetic", impl="ours",
+               config=dict(workload=desc, triangles=scene.n_triangles, width=W, height=H, spp_per_gpu=spp, max_depth=cfg["max_depth"],
+                           integrator="MIS", parallelism="sample slices, replicated scene, NCCL all-reduce of accum" if world > 1 else "single GPU",
+                           l2_policy="working set larger than L2: %.0f MB of path state + %.0f MB of BVH per pass, rewritten every bounce"
+                                     % (4 * (1 << 20) * 250 / 1e6, (r.stats()["bvh_nodes"] * 80 + scene.n_triangles * 48) / 1e6),
+                           timing="CUDA events on the context stream (N=1) / barrier-bracketed wall clock incl. all-reduce, max over ranks (N>1)"),
+               spp_per_s=round(spp * world * args.steps / t_all, 3), rays_per_step=rays_all // args.steps,
+               gpu_launches=launches_all, accel_build_ms=round(accel_ms, 3), clocks=clk, wall_s=round(wall, 3))
+    if rank == 0 and world == 1:
+        # ---- e2e through the C ABI with host buffers
+        h2d = scene.vertices.nbytes + scene.normals.nbytes + scene.texcoords.nbytes + scene.indices.nbytes + scene.material_ids.nbytes + \
+            scene.prim_offsets.nbytes + xf.nbytes + inv.nbytes + (scene.lut.nbytes if scene.lut is not None else 0) + scene.ibl.nbytes
+        d2h = W * H * 16 + W * H * 4
+        color = np.empty((H, W, 4), np.float32); rgba = np.empty((H, W, 4), np.uint8)
+        e_rays, t0 = 0, time.perf_counter()
+        for _ in range(args.steps):
+            r.upload(scene); r.build_accel(xf, inv); r.render(fp)
+            r.readback(abi.AOV_COLOR, color); r.readback(abi.AOV_RGBA8, rgba)
+            st = r.stats(); e_rays += st["rays_extend"] + st["rays_shadow"]
+        e_t = time.perf_counter() - t0
+        out["e2e"] = dict(value=round(e_rays / e_t / 1e6, 2), unit="Mrays/s", h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h),
+                          ms_per_step=round(1e3 * e_t / args.steps, 3), checksum=float(color[..., :3].mean()))
+        # ---- roofline of the traversal kernels: bytes from a counters pass, time from an event-pair pass
+        r.set_option("count_fetches", 1); r.render(fp); sc = r.stats(); r.set_option("count_fetches", 0)
+        r.set_option("time_stages", 1); r.render(fp); stt = r.stats(); r.set_option("time_stages", 0)
+        algo = 80.0 * sc["nodes_fetched"] + 48.0 * sc["tris_fetched"]
+        nrays = sc["rays_extend"] + sc["rays_shadow"]
+        n_trace_launches = max(1, (st["kernel_launches"] - 1) // 1)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        ach = algo / (stt["ms_trace"] / 1e3) / 1e9
+        out["roofline"] = dict(bound="hbm", achieved=round(ach, 1), peak=peak, unit="GB/s", frac=round(ach / peak, 4), traffic=None,
+                               peak_source="MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback",
+                               kernel="k_extend+k_shadow+k_mis (BVH traversal)", trace_ms_per_step=round(stt["ms_trace"], 3),
+                               shade_ms_per_step=round(stt["ms_shade"], 3), step_ms_timed_pass=round(stt["ms_render"], 3),
+                               nodes_per_ray=round(sc["nodes_fetched"] / nrays, 2), tris_per_ray=round(sc["tris_fetched"] / nrays, 2),
+                               bytes_per_ray=round(algo / nrays, 1), bound_mrays=round(peak * 1e9 / (algo / nrays) / 1e6, 1))
+        if not args.no_cpu:
+            vals, info = cpu_arm(scene, cfg, budget_s=args.cpu_budget)
+            out["cpu_baseline"] = dict(value=round(vals[0], 3), unit="Mrays/s", cores=info["cores"], kind=info["kind"], sample=info["sample"],
+                                       spp_per_s=round(info["spp_per_s"], 5))
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    r.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    scene, cfg, desc = make_workload(args.workload)
+    vals, info = cpu_arm(scene, cfg, budget_s=args.cpu_budget, steps=args.steps, warmup=min(args.warmup, 1))
+    v = float(np.mean(vals))
+    out = dict(metric="Mrays/s", value=round(v, 3), unit="Mrays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
+               ms_per_step=round(1e3 * info["seconds"], 3), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
+               data="synthetic", impl="reference",
+               config=dict(workload=desc, triangles=scene.n_triangles, width=cfg["width"], height=cfg["height"], max_depth=cfg["max_depth"], integrator="MIS"),
+               cpu_baseline=dict(value=round(v, 3), unit="Mrays/s", cores=info["cores"], kind=info["kind"], sample=info["sample"]),
+               e2e=dict(value=round(v, 3), unit="Mrays/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0,
+               note="reference's own device headers compiled for the host (oracle/_ref) with the reconstructed raygen/closest-hit and a CPU BVH; "
+                    "the reference through OptiX/RT cores is unavailable on this box")
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--cpu-budget", type=float, default=12.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank, world)
+    else:
+        gpu_arm(args, rank, world, local)
+
+
+if __name__ == "__main__":
+    main()

@@ -68,6 +68,7 @@ void hj_destroy(hj_ctx* c) {
                       &c->wf.q_shadow, &c->wf.q_mis, &c->wf.sh_o, &c->wf.sh_d, &c->wf.sh_c, &c->wf.mi_o, &c->wf.mi_d, &c->wf.mi_a, &c->wf.mi_t, &c->wf.counters,
                       &c->aov_color, &c->aov_albedo, &c->aov_normal, &c->aov_rgba8, &c->aov_accum, &c->aov_path_rad, &c->aov_path_ids};
     for (DevBuf* b : bufs) b->release();
+    for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
     delete c;

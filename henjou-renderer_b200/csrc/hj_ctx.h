@@ -69,6 +69,8 @@ struct hj_ctx {
     DevBuf aov_color, aov_albedo, aov_normal, aov_rgba8, aov_accum, aov_path_rad, aov_path_ids;
     uint32_t fb_w = 0, fb_h = 0;
     hj_stats stats{};
+    // option "time_stages": event pairs around every traversal (kind 0) and shading (kind 1) launch of the last frame
+    std::vector<cudaEvent_t> ev_pool; std::vector<int> ev_kind;
     // multi-GPU
     NcclApi* nccl = nullptr; void* comm = nullptr; int rank = 0, nranks = 1;
 };

@@ -440,6 +440,16 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     const bool count = c->opt_count_fetches != 0;
     uint64_t launches = 0;
 
+    const bool timed = c->opt_time_stages != 0;
+    c->ev_kind.clear();
+    auto mark_begin = [&](int kind) {
+        if (!timed) return;
+        const size_t i = 2 * c->ev_kind.size();
+        while (c->ev_pool.size() < i + 2) { cudaEvent_t e; cudaEventCreate(&e); c->ev_pool.push_back(e); }
+        c->ev_kind.push_back(kind);
+        cudaEventRecord(c->ev_pool[i], st);
+    };
+    auto mark_end = [&]() { if (timed) cudaEventRecord(c->ev_pool[2 * c->ev_kind.size() - 1], st); };
     HJ_CUDA(c, cudaEventRecord(c->ev0, st));
     HJ_CUDA(c, cudaMemsetAsync(w.counters.p, 0, sizeof(WfCounters), st));
     HJ_CUDA(c, cudaMemsetAsync(c->aov_accum.p, 0, fb, st));
@@ -451,20 +461,28 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
         launches += 2;
         int cur = 0;
         for (int depth = 0; depth < fp->max_depth; depth++) {
+            mark_begin(0);
             if (count) k_extend<true><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur);
             else k_extend<false><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur);
+            mark_end();
+            mark_begin(1);
             if (fp->integrator == HJ_INTEGRATOR_PT) k_shade<HJ_INTEGRATOR_PT><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur, depth, s0);
             else if (fp->integrator == HJ_INTEGRATOR_NEE) k_shade<HJ_INTEGRATOR_NEE><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur, depth, s0);
             else k_shade<HJ_INTEGRATOR_MIS><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur, depth, s0);
+            mark_end();
             launches += 2;
             if (fp->integrator != HJ_INTEGRATOR_PT) {
+                mark_begin(0);
                 if (count) k_shadow<true><<<grid, WF_THREADS, 0, st>>>(c->S, P);
                 else k_shadow<false><<<grid, WF_THREADS, 0, st>>>(c->S, P);
+                mark_end();
                 launches++;
             }
             if (fp->integrator == HJ_INTEGRATOR_MIS) {
+                mark_begin(0);
                 if (count) k_mis<true><<<grid, WF_THREADS, 0, st>>>(c->S, F, P);
                 else k_mis<false><<<grid, WF_THREADS, 0, st>>>(c->S, F, P);
+                mark_end();
                 launches++;
             }
             k_swap_queues<<<1, 1, 0, st>>>(P.cnt, cur);
@@ -500,5 +518,11 @@ int hj_wavefront_stats(hj_ctx* c) {
     c->stats.rays_extend = h.rays_extend; c->stats.rays_shadow = h.rays_shadow;
     c->stats.nodes_fetched = h.nodes; c->stats.tris_fetched = h.tris;
     float ms = 0; if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->stats.ms_render = ms;
+    double tt = 0, ts = 0;
+    for (size_t i = 0; i < c->ev_kind.size(); i++) {
+        float m = 0; cudaEventElapsedTime(&m, c->ev_pool[2 * i], c->ev_pool[2 * i + 1]);
+        (c->ev_kind[i] == 0 ? tt : ts) += m;
+    }
+    c->stats.ms_trace = (float)tt; c->stats.ms_shade = (float)ts;
     return HJ_OK;
 }
