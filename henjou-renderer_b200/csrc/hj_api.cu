@@ -64,10 +64,14 @@ void hj_destroy(hj_ctx* c) {
                       &c->bvh.keys, &c->bvh.keys_alt, &c->bvh.vals, &c->bvh.vals_alt, &c->bvh.block_hist, &c->bvh.blo, &c->bvh.bhi, &c->bvh.left,
                       &c->bvh.right, &c->bvh.parent, &c->bvh.rfirst, &c->bvh.rlast, &c->bvh.flags, &c->bvh.bounds, &c->bvh.queue_a, &c->bvh.queue_b,
                       &c->bvh.counters, &c->bvh.nodes, &c->bvh.btris,
-                      &c->wf.ray_o, &c->wf.ray_d, &c->wf.hit, &c->wf.thr, &c->wf.L, &c->wf.rng_depth, &c->wf.dbg, &c->wf.q_extend[0], &c->wf.q_extend[1],
-                      &c->wf.q_shadow, &c->wf.q_mis, &c->wf.sh_o, &c->wf.sh_d, &c->wf.sh_c, &c->wf.mi_o, &c->wf.mi_d, &c->wf.mi_a, &c->wf.mi_t, &c->wf.counters,
                       &c->aov_color, &c->aov_albedo, &c->aov_normal, &c->aov_rgba8, &c->aov_accum, &c->aov_path_rad, &c->aov_path_ids};
     for (DevBuf* b : bufs) b->release();
+    for (WavefrontState& w : c->wf) {
+        for (DevBuf* b : w.all) if (b) b->release();
+        if (w.stream) cudaStreamDestroy(w.stream);
+        if (w.ev_acc) cudaEventDestroy(w.ev_acc);
+    }
+    if (c->ev_frame) cudaEventDestroy(c->ev_frame);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
@@ -79,7 +83,9 @@ int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
     if (!strcmp(key, "count_fetches")) c->opt_count_fetches = value != 0;
     else if (!strcmp(key, "time_stages")) c->opt_time_stages = value != 0;
     else if (!strcmp(key, "paths_per_pass")) c->opt_paths_per_pass = value;
-    else if (!strcmp(key, "leaf_max")) { HJ_REQUIRE(c, value >= 1 && value <= 4, HJ_ERR_INVALID, "hj_set_option: leaf_max must be 1..4"); c->opt_leaf_max = (int)value; }
+    else if (!strcmp(key, "trace_blocks_per_sm")) { HJ_REQUIRE(c, value >= 0 && value <= 32, HJ_ERR_INVALID, "hj_set_option: trace_blocks_per_sm must be 0 (auto) .. 32"); c->opt_trace_blocks_per_sm = (int)value; }
+    else if (!strcmp(key, "pipelines")) { HJ_REQUIRE(c, value >= 1 && value <= HJ_MAX_PIPES, HJ_ERR_INVALID, "hj_set_option: pipelines must be 1..8"); c->opt_pipelines = (int)value; }
+    else if (!strcmp(key, "leaf_max")) { HJ_REQUIRE(c, value >= 1 && value <= 3, HJ_ERR_INVALID, "hj_set_option: leaf_max must be 1..3"); c->opt_leaf_max = (int)value; }
     else { c->err = std::string("hj_set_option: unknown option '") + key + "'"; return HJ_ERR_INVALID; }
     return HJ_OK;
 }

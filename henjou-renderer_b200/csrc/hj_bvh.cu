@@ -310,8 +310,8 @@ __global__ void k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32
         if (k < 0) continue;
         const uint32_t id = ch[k];
         const uint32_t cnt = bn_count(a, id);
-        if (id < (uint32_t)(a.n - 1) && cnt > a.leaf_max) { imask |= 1u << s; n_int++; }
-        else { meta[s] = (cnt << 5) | n_tri; n_tri += cnt; }
+        if (id < (uint32_t)(a.n - 1) && cnt > a.leaf_max) { imask |= 1u << s; n_int++; meta[s] = (1u << 5) | (24u + (uint32_t)s); }
+        else { meta[s] = (((1u << cnt) - 1u) << 5) | n_tri; n_tri += cnt; }
         for (int ax = 0; ax < 3; ax++) {
             int ql = (int)floorf((clo[k][ax] - lo[ax]) / scale[ax]);
             ql = max(0, min(255, ql));
@@ -340,7 +340,7 @@ __global__ void k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32
         if (k < 0) continue;
         if (imask & (1u << s)) { qout[qbase + r] = make_uint2(ch[k], child_base + r); r++; }
         else {
-            const uint32_t first = bn_first(a, ch[k]), cnt = meta[s] >> 5, off = meta[s] & 31u;
+            const uint32_t first = bn_first(a, ch[k]), cnt = bn_count(a, ch[k]), off = meta[s] & 31u;
             for (uint32_t j = 0; j < cnt; j++) {
                 const uint32_t prim = a.sorted[first + j];
                 const float4* P = a.tri_pos + 3 * (size_t)prim;
@@ -423,12 +423,12 @@ int hj_bvh_build(hj_ctx* c, int mode) {
     HJ_CUDA(c, cudaGetLastError());
     float ms = 0; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     if (cnt[1] != n) { c->err = "hj_accel_build: internal error, leaf triangles != scene triangles"; return HJ_ERR_INVALID; }
-    if (depth > HJ_STACK) {
+    if (2 * depth > HJ_STACK) {
         char b[160]; snprintf(b, sizeof b, "hj_accel_build: wide BVH depth %u exceeds the traversal stack (%d)", depth, HJ_STACK);
         c->err = b; return HJ_ERR_INVALID;
     }
     B.n_nodes = cnt[0]; B.depth = depth;
     c->S.nodes = B.nodes.as<uint4>(); c->S.btris = B.btris.as<float4>();
-    c->stats.ms_accel = ms; c->stats.bvh_nodes = B.n_nodes; c->stats.bvh_node_bytes = 80;
+    c->stats.ms_accel = ms; c->stats.bvh_nodes = B.n_nodes; c->stats.bvh_node_bytes = 80; c->stats.bvh_depth = depth;
     return HJ_OK;
 }

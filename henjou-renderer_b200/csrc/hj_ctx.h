@@ -37,13 +37,19 @@ struct BvhState {
     bool have_topology = false;
 };
 
+#define HJ_MAX_PIPES 8
+// One wavefront pipeline: the path state of one pass in flight. Several pipelines run passes concurrently on their
+// own streams so that the tail of one persistent traversal kernel overlaps the next pipeline's work.
 struct WavefrontState {
     uint32_t capacity = 0;        // path slots
+    cudaStream_t stream = nullptr; cudaEvent_t ev_acc = nullptr;
     DevBuf ray_o, ray_d, hit, thr, L, rng_depth, dbg;   // per-slot state (SoA)
     DevBuf q_extend[2], q_shadow, q_mis;                 // queues
     DevBuf sh_o, sh_d, sh_c;      // shadow ray payload per slot: origin+tmax, dir, contribution
     DevBuf mi_o, mi_d, mi_a, mi_t;   // MIS ray payload per slot
     DevBuf counters;              // device-side queue counters + ray statistics
+    DevBuf* all[20] = {&ray_o, &ray_d, &hit, &thr, &L, &rng_depth, &dbg, &q_extend[0], &q_extend[1], &q_shadow, &q_mis,
+                       &sh_o, &sh_d, &sh_c, &mi_o, &mi_d, &mi_a, &mi_t, &counters, nullptr};
 };
 
 struct NcclApi;
@@ -54,7 +60,7 @@ struct hj_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;
     // options
-    int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3;
+    int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3, opt_trace_blocks_per_sm = 0, opt_pipelines = 4;
     int64_t opt_paths_per_pass = 0;
     // scene
     bool have_scene = false, have_accel = false, have_frame = false;
@@ -63,7 +69,9 @@ struct hj_ctx {
     DevBuf d_xf, d_inv_xf, d_materials, d_textures, d_texels, d_srgb, d_light_ids, d_light_em, d_ibl, d_lut;
     DevBuf d_tri_pos, d_tri_attr;
     BvhState bvh;
-    WavefrontState wf;
+    WavefrontState wf[HJ_MAX_PIPES];
+    int n_pipes_used = 0;
+    cudaEvent_t ev_frame = nullptr;
     // frame
     hj_frame_params fp{};
     DevBuf aov_color, aov_albedo, aov_normal, aov_rgba8, aov_accum, aov_path_rad, aov_path_ids;

@@ -5,7 +5,11 @@
 // Node (80 B = five 16-byte loads; built by hj_bvh.cu):
 //   q0: origin.xyz (float bits) | ex | ey<<8 | ez<<16 | imask<<24      (e* = biased float exponents of the grid step)
 //   q1: child_base (first internal child node), tri_base (first triangle of this node's leaves), meta[0..3], meta[4..7]
-//       meta[s] = (count<<5) | offset for a leaf slot (count 1..4 triangles at tri_base+offset), 0 otherwise
+//       meta[s] = (unary count << 5) | offset   leaf slot: 1..3 triangles at tri_base+offset (count bits 001/011/111)
+//               = (1 << 5) | (24 + s)           internal child in slot s (child node = child_base + popc(imask below s))
+//               = 0                              empty slot
+//       so `(meta >> 5) << (meta & 31)` drops a child's hit straight into a 32-bit mask: bits 0..23 = triangles
+//       of this node, bits 24..31 = internal children (Ylitie, Karras, Laine 2017)
 //   q2: qlo.x[0..7] qlo.y[0..7]   q3: qlo.z[0..7] qhi.x[0..7]   q4: qhi.y[0..7] qhi.z[0..7]      (8-bit grid coordinates)
 // Child slots are assigned at build time by octant (slot bit k set = child on the + side of axis k), so
 // `slot ^ ray_octant` orders children front to back without sorting (Ylitie et al. 2017).
@@ -16,7 +20,11 @@
 #pragma once
 #include "hj_scene.cuh"
 
-#define HJ_STACK 64
+#define HJ_STACK 96          // local-memory part of the traversal stack
+#ifndef HJ_SSTACK
+#define HJ_SSTACK 12         // shared-memory part (entries per thread)
+#endif
+#define HJ_TRACE_THREADS 128 // block size of every kernel that traverses
 
 struct RayPrep {
     float3 o;
@@ -67,96 +75,120 @@ HJ_DI bool tri_test(const RayPrep& r, const float3& p0, const float3& p1, const 
 
 struct Hit { float t, b1, b2; uint32_t prim; };   // prim == 0xffffffff: miss
 
-// bit s of `m` moves to bit s^oct: three conditional swaps
-HJ_DI uint32_t perm_mask(uint32_t m, uint32_t oct) {
-    if (oct & 1u) m = ((m & 0x55u) << 1) | ((m >> 1) & 0x55u);
-    if (oct & 2u) m = ((m & 0x33u) << 2) | ((m >> 2) & 0x33u);
-    if (oct & 4u) m = ((m & 0x0fu) << 4) | ((m >> 4) & 0x0fu);
-    return m;
-}
+// Traversal state of one ray, advanced in two kinds of steps so that a warp can batch them: node_visit() intersects the
+// 8 quantised child boxes of the nearest pending inner child; tri_one() tests one pending triangle. Stack entries are
+// 8-byte groups (child_base, inner-hit bits 24..31 | imask).
+struct Trav {
+    RayPrep r; float tmin, tmax; Hit best;
+    uint2 ng, tg; int sp; uint32_t oct_inv;
+    uint2* sstack;                 // HJ_SSTACK entries in shared memory, strided by the block size (bank-conflict free)
+    uint2 stack[HJ_STACK];         // overflow beyond HJ_SSTACK: local memory
+    HJ_DI void push(const uint2 v) { if (sp < HJ_SSTACK) sstack[sp * HJ_TRACE_THREADS] = v; else stack[sp - HJ_SSTACK] = v; sp++; }
+    HJ_DI uint2 pop() { sp--; return sp < HJ_SSTACK ? sstack[sp * HJ_TRACE_THREADS] : stack[sp - HJ_SSTACK]; }
 
-// Intersects the 8 quantised child boxes of one node with the ray; returns the slot mask of children whose
-// box overlaps [tmin, tcur]. Conservative: the slab bounds are widened by a slack proportional to the
-// magnitudes involved, so rounding in this test can never cull a triangle the (exact) triangle test accepts.
-HJ_DI uint32_t node_children_hit(const uint4 q0, const uint4 q2, const uint4 q3, const uint4 q4, uint32_t valid,
-                                 const RayPrep& r, float tmin, float tcur) {
-    const float sx = __uint_as_float((q0.w & 0xffu) << 23), sy = __uint_as_float(((q0.w >> 8) & 0xffu) << 23),
-                sz = __uint_as_float(((q0.w >> 16) & 0xffu) << 23);
-    const float ax = sx * r.idir.x, ay = sy * r.idir.y, az = sz * r.idir.z;
-    const float ox = (__uint_as_float(q0.x) - r.o.x) * r.idir.x, oy = (__uint_as_float(q0.y) - r.o.y) * r.idir.y,
-                oz = (__uint_as_float(q0.z) - r.o.z) * r.idir.z;
-    const float slack = 2e-6f * (fabsf(ox) + fabsf(oy) + fabsf(oz) + 255.0f * (fabsf(ax) + fabsf(ay) + fabsf(az)));
-    // near/far planes per axis by ray sign
-    const uint32_t lox[2] = {q2.x, q2.y}, loy[2] = {q2.z, q2.w}, loz[2] = {q3.x, q3.y};
-    const uint32_t hix[2] = {q3.z, q3.w}, hiy[2] = {q4.x, q4.y}, hiz[2] = {q4.z, q4.w};
-    const bool nx = (r.oct & 1u) != 0, ny = (r.oct & 2u) != 0, nz = (r.oct & 4u) != 0;
-    uint32_t mask = 0;
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-        const uint32_t nearx = nx ? hix[h] : lox[h], farx = nx ? lox[h] : hix[h];
-        const uint32_t neary = ny ? hiy[h] : loy[h], fary = ny ? loy[h] : hiy[h];
-        const uint32_t nearz = nz ? hiz[h] : loz[h], farz = nz ? loz[h] : hiz[h];
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const float tnx = (float)((nearx >> (8 * j)) & 0xffu) * ax + ox, tfx = (float)((farx >> (8 * j)) & 0xffu) * ax + ox;
-            const float tny = (float)((neary >> (8 * j)) & 0xffu) * ay + oy, tfy = (float)((fary >> (8 * j)) & 0xffu) * ay + oy;
-            const float tnz = (float)((nearz >> (8 * j)) & 0xffu) * az + oz, tfz = (float)((farz >> (8 * j)) & 0xffu) * az + oz;
-            const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin)) - slack;
-            const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tcur)) + slack;
-            if (tn <= tf) mask |= 1u << (4 * h + j);
-        }
+    HJ_DI void init(const float3& o, const float3& d, float tmin_, float tmax_) {
+        r = prep_ray(o, d); tmin = tmin_; tmax = tmax_;
+        best.t = tmax_; best.b1 = best.b2 = 0.0f; best.prim = 0xffffffffu;
+        ng = make_uint2(0u, 0x80000000u);     // the root, as the only inner hit of a virtual parent
+        tg = make_uint2(0u, 0u); sp = 0; oct_inv = r.oct ^ 7u;
     }
-    return mask & valid;
-}
+    HJ_DI bool has_inner() const { return ng.y > 0x00ffffffu; }
+    HJ_DI bool has_tris() const { return tg.y != 0u; }
+    // makes an inner group current if there is one (pop); false: nothing left to visit
+    HJ_DI bool fetch_group() {
+        if (has_inner()) return true;
+        if (sp == 0) return false;
+        ng = pop();
+        return true;
+    }
 
-HJ_DI uint32_t meta_of(const uint4& q1, int s) { return ((s < 4 ? q1.z : q1.w) >> (8 * (s & 3))) & 0xffu; }
-
-// Closest hit in (tmin,tmax); ties on t -> lower global primitive id. COUNT: fetch counters for the roofline.
-template <bool ANY, bool COUNT>
-HJ_DI Hit traverse(const DevScene& S, const float3& o, const float3& d, float tmin, float tmax, uint32_t& n_nodes, uint32_t& n_tris) {
-    Hit best; best.t = tmax; best.b1 = best.b2 = 0.0f; best.prim = 0xffffffffu;
-    const RayPrep r = prep_ray(o, d);
-    uint2 stack[HJ_STACK];
-    int sp = 0;
-    uint32_t node = 0;
-    while (true) {
+    // Visits the nearest remaining inner child of the current group (requires has_inner()): loads its 80-byte node and
+    // intersects the 8 child boxes; leaves the inner hits in ng and the triangle hits in tg.
+    template <bool COUNT>
+    HJ_DI void node_visit(const DevScene& S, uint32_t& n_nodes) {
+        const uint32_t k = 31u - (uint32_t)__clz(ng.y);          // highest bit = nearest (slots permuted by the ray octant)
+        ng.y &= ~(1u << k);
+        const uint32_t slot = (k - 24u) ^ oct_inv;
+        const uint32_t node = ng.x + __popc(ng.y & 0xffu & ((1u << slot) - 1u));
+        if (ng.y > 0x00ffffffu) push(ng);
         const uint4* N = S.nodes + 5 * (size_t)node;
         const uint4 q0 = __ldg(N), q1 = __ldg(N + 1), q2 = __ldg(N + 2), q3 = __ldg(N + 3), q4 = __ldg(N + 4);
         if (COUNT) n_nodes++;
-        const uint32_t imask = q0.w >> 24;
-        uint32_t leafmask = 0;
-#pragma unroll
-        for (int s = 0; s < 8; s++) if (meta_of(q1, s)) leafmask |= 1u << s;
+        const float sx = __uint_as_float((q0.w & 0xffu) << 23), sy = __uint_as_float(((q0.w >> 8) & 0xffu) << 23),
+                    sz = __uint_as_float(((q0.w >> 16) & 0xffu) << 23);
+        const float ax = sx * r.idir.x, ay = sy * r.idir.y, az = sz * r.idir.z;
+        const float ox = (__uint_as_float(q0.x) - r.o.x) * r.idir.x, oy = (__uint_as_float(q0.y) - r.o.y) * r.idir.y,
+                    oz = (__uint_as_float(q0.z) - r.o.z) * r.idir.z;
+        // Plane distance t = q*a + o with q an 8-bit grid coordinate. q enters as the float 2^23+q (one PRMT, no
+        // int->float conversion) and the 2^23*a is folded into o: t = fma(2^23+q, a, o - 2^23 a). That costs half a grid
+        // cell of accuracy, so every slab is widened by one cell |a| plus a slack proportional to the magnitudes involved:
+        // rounding here can never cull a triangle that the (exact) triangle test accepts.
+        const float slack = 2e-6f * (fabsf(ox) + fabsf(oy) + fabsf(oz) + 255.0f * (fabsf(ax) + fabsf(ay) + fabsf(az)));
+        const float bx = 8388608.0f * ax, by = 8388608.0f * ay, bz = 8388608.0f * az;
+        const float oxn = (ox - slack - fabsf(ax)) - bx, oyn = (oy - slack - fabsf(ay)) - by, ozn = (oz - slack - fabsf(az)) - bz;
+        const float oxf = (ox + slack + fabsf(ax)) - bx, oyf = (oy + slack + fabsf(ay)) - by, ozf = (oz + slack + fabsf(az)) - bz;
         const float tcur = (best.prim != 0xffffffffu) ? best.t : tmax;
-        const uint32_t hits = node_children_hit(q0, q2, q3, q4, imask | leafmask, r, tmin, tcur);
-        uint32_t lh = hits & leafmask;
-        while (lh) {
-            const int s = __ffs(lh) - 1; lh &= lh - 1;
-            const uint32_t m = meta_of(q1, s);
-            const uint32_t first = q1.y + (m & 31u), cnt = m >> 5;
-            for (uint32_t k = 0; k < cnt; k++) {
-                const float4* T = S.btris + 3 * (size_t)(first + k);
-                const float4 v0 = __ldg(T), v1 = __ldg(T + 1), v2 = __ldg(T + 2);
-                if (COUNT) n_tris++;
-                float t, b1, b2;
-                if (tri_test(r, f3(v0), f3(v1), f3(v2), tmin, tmax, t, b1, b2)) {
-                    const uint32_t p = __float_as_uint(v0.w);
-                    if (ANY) { best.t = t; best.b1 = b1; best.b2 = b2; best.prim = p; return best; }
-                    if (best.prim == 0xffffffffu || t < best.t || (t == best.t && p < best.prim)) { best.t = t; best.b1 = b1; best.b2 = b2; best.prim = p; }
-                }
+        const bool nx = (r.oct & 1u) != 0, ny = (r.oct & 2u) != 0, nz = (r.oct & 4u) != 0;
+        const uint32_t oct_inv4 = oct_inv * 0x01010101u;
+        uint32_t hitmask = 0;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const uint32_t lox = h ? q2.y : q2.x, loy = h ? q2.w : q2.z, loz = h ? q3.y : q3.x;
+            const uint32_t hix = h ? q3.w : q3.z, hiy = h ? q4.y : q4.x, hiz = h ? q4.w : q4.z;
+            const uint32_t meta4 = h ? q1.w : q1.z;
+            // four metas at once: inner children (bit index 24..31 = 0b11xxx) get their slot XORed with the octant
+            const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+            const uint32_t inner_mask4 = (is_inner4 >> 4) * 0x07u;
+            const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
+            const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+            const uint32_t nearx = nx ? hix : lox, farx = nx ? lox : hix;
+            const uint32_t neary = ny ? hiy : loy, fary = ny ? loy : hiy;
+            const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint32_t sel = 0x7650u | (uint32_t)j;
+                const float tnx = __fmaf_rn(__uint_as_float(__byte_perm(nearx, 0x4B000000u, sel)), ax, oxn);
+                const float tny = __fmaf_rn(__uint_as_float(__byte_perm(neary, 0x4B000000u, sel)), ay, oyn);
+                const float tnz = __fmaf_rn(__uint_as_float(__byte_perm(nearz, 0x4B000000u, sel)), az, ozn);
+                const float tfx = __fmaf_rn(__uint_as_float(__byte_perm(farx, 0x4B000000u, sel)), ax, oxf);
+                const float tfy = __fmaf_rn(__uint_as_float(__byte_perm(fary, 0x4B000000u, sel)), ay, oyf);
+                const float tfz = __fmaf_rn(__uint_as_float(__byte_perm(farz, 0x4B000000u, sel)), az, ozf);
+                const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+                const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tcur));
+                const uint32_t bits = (child_bits4 >> (8 * j)) & 0xffu, idx = (bit_index4 >> (8 * j)) & 0xffu;
+                if (tn <= tf) hitmask |= bits << idx;      // empty slots have meta = 0
             }
         }
-        uint32_t ih = hits & imask, base = q1.x, im = imask;
-        if (!ih) {
-            if (sp == 0) break;
-            const uint2 e = stack[--sp];
-            base = e.x; im = e.y >> 8; ih = e.y & 0xffu;
-        }
-        // nearest remaining child of the group: lowest set bit after permuting slots by the ray octant
-        const uint32_t s = (uint32_t)(__ffs(perm_mask(ih, r.oct)) - 1) ^ r.oct;
-        ih &= ~(1u << s);
-        if (ih && sp < HJ_STACK) stack[sp++] = make_uint2(base, (im << 8) | ih);
-        node = base + __popc(im & ((1u << s) - 1u));
+        ng = make_uint2(q1.x, (hitmask & 0xff000000u) | (q0.w >> 24));
+        tg = make_uint2(q1.y, hitmask & 0x00ffffffu);
     }
-    return best;
+
+    // Tests one pending triangle (requires has_tris()). ANY: returns true on the first accepted hit.
+    template <bool ANY, bool COUNT>
+    HJ_DI bool tri_one(const DevScene& S, uint32_t& n_tris) {
+        const uint32_t j = 31u - (uint32_t)__clz(tg.y);
+        tg.y &= ~(1u << j);
+        const float4* T = S.btris + 3 * (size_t)(tg.x + j);
+        const float4 v0 = __ldg(T), v1 = __ldg(T + 1), v2 = __ldg(T + 2);
+        if (COUNT) n_tris++;
+        float t, b1, b2;
+        if (tri_test(r, f3(v0), f3(v1), f3(v2), tmin, tmax, t, b1, b2)) {
+            const uint32_t p = __float_as_uint(v0.w);
+            if (ANY) { best.t = t; best.b1 = b1; best.b2 = b2; best.prim = p; return true; }
+            if (best.prim == 0xffffffffu || t < best.t || (t == best.t && p < best.prim)) { best.t = t; best.b1 = b1; best.b2 = b2; best.prim = p; }
+        }
+        return false;
+    }
+};
+
+// whole-ray convenience wrapper (batch queries, tests): no warp batching
+template <bool ANY, bool COUNT>
+HJ_DI Hit traverse(const DevScene& S, const float3& o, const float3& d, float tmin, float tmax, uint32_t& n_nodes, uint32_t& n_tris) {
+    __shared__ uint2 s_stack[(HJ_SSTACK ? HJ_SSTACK : 1) * HJ_TRACE_THREADS];
+    Trav t; t.sstack = s_stack + threadIdx.x; t.init(o, d, tmin, tmax);
+    while (t.fetch_group()) {
+        t.node_visit<COUNT>(S, n_nodes);
+        while (t.has_tris()) if (t.tri_one<ANY, COUNT>(S, n_tris)) return t.best;
+    }
+    return t.best;
 }

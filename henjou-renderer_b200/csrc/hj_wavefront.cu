@@ -17,7 +17,9 @@
 
 struct WfCounters {
     uint32_t n_extend[2]; uint32_t n_shadow, n_mis;
+    uint32_t next[4];             // work-fetch cursors of the persistent traversal kernels (extend, shadow, mis)
     unsigned long long rays_extend, rays_shadow, nodes, tris;
+    uint32_t max_nodes, max_tris;
 };
 
 struct FrameK {
@@ -84,31 +86,6 @@ __global__ void __launch_bounds__(WF_THREADS) k_raygen(FrameK F, WfPtrs P, uint3
         // every first-iteration roulette passes (throughput 1 > any draw), so the queue is the identity
         P.q_ext[0][slot] = alive ? slot : 0xffffffffu;
     }
-}
-
-// ---------------------------------------------------------------------------------------------- extend
-template <bool COUNT>
-__global__ void __launch_bounds__(WF_THREADS) k_extend(DevScene S, FrameK F, WfPtrs P, int cur) {
-    const uint32_t n = P.cnt->n_extend[cur];
-    const uint32_t stride = gridDim.x * blockDim.x;
-    uint32_t nn = 0, nt = 0, nr = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const uint32_t slot = P.q_ext[cur][i];
-        if (slot == 0xffffffffu) continue;
-        const float4 o = P.ray_o[slot], d = P.ray_d[slot];
-        const Hit h = traverse<false, COUNT>(S, f3(o), f3(d), 0.001f, 1e16f, nn, nt);
-        P.hit[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.prim));
-        nr++;
-        if (F.debug) {
-            uint2 g = P.dbg[slot];
-            if (P.L[slot].w == 0.0f) g.x = h.prim;     // first ray of the path
-            g.y = (g.y ^ (h.prim + 1u)) * 0x01000193u;
-            P.dbg[slot] = g;
-        }
-        P.L[slot].w += 1.0f;
-    }
-    warp_add64(&P.cnt->rays_extend, nr);
-    if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
 }
 
 // ---------------------------------------------------------------------------------------------- light sampling
@@ -239,75 +216,152 @@ __global__ void __launch_bounds__(WF_THREADS) k_shade(DevScene S, FrameK F, WfPt
     }
 }
 
-// ---------------------------------------------------------------------------------------------- shadow / MIS rays
-// TraceOcculution (rt.h:15-41): any hit in (1e-3, dist-1e-3) discards the light sample.
-template <bool COUNT>
-__global__ void __launch_bounds__(WF_THREADS) k_shadow(DevScene S, WfPtrs P) {
-    const uint32_t n = P.cnt->n_shadow;
-    const uint32_t stride = gridDim.x * blockDim.x;
-    uint32_t nn = 0, nt = 0, nr = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const uint32_t slot = P.q_shadow[i];
-        const float4 o = P.sh_o[slot], d = P.sh_d[slot];
-        const Hit h = traverse<true, COUNT>(S, f3(o), f3(d), 0.001f, o.w, nn, nt);
-        float4 L = P.L[slot];
-        if (h.prim == 0xffffffffu) { const float4 c = P.sh_c[slot]; L.x += c.x; L.y += c.y; L.z += c.z; }
-        L.w += 1.0f;
-        P.L[slot] = L;
-        nr++;
+// ---------------------------------------------------------------------------------------------- traversal kernels
+// One persistent kernel per ray type (the reference's two optixTrace call sites, rt.h:53 RayTrace and rt.h:25
+// TraceOcculution, plus the MIS emitter ray rt.h:389). Warps fetch rays from the queue dynamically: a lane whose ray
+// has finished idles only until the warp has lost LOST_MAX lane-iterations, then the warp refills every idle lane
+// with one warp-aggregated atomic — this keeps the SIMD lanes busy although ray lengths differ by 10x.
+#ifndef HJ_MINB
+#define HJ_MINB 8
+#endif
+#ifndef REFILL_MIN
+#define REFILL_MIN 8
+#endif
+#ifndef TRACE_BURST
+#define TRACE_BURST 4
+#endif
+#ifndef TRI_BATCH
+#define TRI_BATCH 8
+#endif
+//#define REFILL_MIN 8     // idle lanes before a warp fetches new rays
+// REFILL_MIN: idle lanes before a warp fetches new rays; TRACE_BURST: phases between refill checks;
+// TRI_BATCH: lanes with pending triangles that trigger a triangle phase
+
+HJ_DI void finish_extend(const FrameK& F, const WfPtrs& P, uint32_t slot, const Hit& h) {
+    P.hit[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.prim));
+    float4 L = P.L[slot];
+    if (F.debug) {
+        uint2 g = P.dbg[slot];
+        if (L.w == 0.0f) g.x = h.prim;     // first ray of the path
+        g.y = (g.y ^ (h.prim + 1u)) * 0x01000193u;
+        P.dbg[slot] = g;
     }
-    warp_add64(&P.cnt->rays_shadow, nr);
-    if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
+    L.w += 1.0f;
+    P.L[slot] = L;
+}
+// TraceOcculution (rt.h:15-41): any hit in (1e-3, dist-1e-3) discards the light sample
+HJ_DI void finish_shadow(const WfPtrs& P, uint32_t slot, const Hit& h) {
+    float4 L = P.L[slot];
+    if (h.prim == 0xffffffffu) { const float4 c = P.sh_c[slot]; L.x += c.x; L.y += c.y; L.z += c.z; }
+    L.w += 1.0f;
+    P.L[slot] = L;
+}
+// the extra BSDF-sampled ray of MIS (rt.h:383-420): emitter hit weighted by the balance heuristic, sky unweighted
+HJ_DI void finish_mis(const DevScene& S, const FrameK& F, const WfPtrs& P, uint32_t slot, const Hit& h) {
+    const float4 oq = P.mi_o[slot], dq = P.mi_d[slot], aq = P.mi_a[slot];
+    const float3 org = f3(oq), wi = f3(dq), f = f3(aq), thr = f3(P.mi_t[slot]);
+    const float c1 = oq.w, ppdf = dq.w;
+    const float4 Lq = P.L[slot];
+    float3 L = f3(Lq);
+    if (h.prim != 0xffffffffu) {
+        const float4 a3 = S.tri_attr[4 * (size_t)h.prim + 3];
+        const DevMaterial& m = S.materials[__float_as_uint(a3.w)];
+        if (m.is_light) {
+            const float4* Pp = S.tri_pos + 3 * (size_t)h.prim; const float4* A = S.tri_attr + 4 * (size_t)h.prim;
+            const float b0 = 1.0f - h.b1 - h.b2;
+            const float3 pos = b0 * f3(Pp[0]) + h.b1 * f3(Pp[1]) + h.b2 * f3(Pp[2]);
+            const float3 ln = normalize(b0 * f3(A[0]) + h.b1 * f3(A[1]) + h.b2 * f3(A[2]));
+            const float3 em = f3(m.emission[0], m.emission[1], m.emission[2]);
+            const float c2 = absdot(-wi, ln);
+            const float dist = length(pos - org);
+            const float invG = dist * dist / c2;
+            const float lpdf = (aq.w != 0.0f) ? 0.0f : light_pdf_area(S, h.prim) * invG;
+            const float w = ppdf / (ppdf + lpdf);
+            L += thr * w * c1 * em * f / ppdf;
+        }
+    } else {
+        const float3 em = sky_radiance(S, wi, F.ibl);
+        L += thr * f * c1 * em / ppdf;
+    }
+    if (F.debug) { uint2 g = P.dbg[slot]; g.y = (g.y ^ (h.prim + 1u)) * 0x01000193u; P.dbg[slot] = g; }
+    P.L[slot] = f4(L, Lq.w + 1.0f);
 }
 
-// The extra BSDF-sampled ray of MIS (rt.h:383-420): emitter hit weighted by the balance heuristic, sky unweighted.
-template <bool COUNT>
-__global__ void __launch_bounds__(WF_THREADS) k_mis(DevScene S, FrameK F, WfPtrs P) {
-    const uint32_t n = P.cnt->n_mis;
-    const uint32_t stride = gridDim.x * blockDim.x;
-    uint32_t nn = 0, nt = 0, nr = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const uint32_t slot = P.q_mis[i];
-        const float4 oq = P.mi_o[slot], dq = P.mi_d[slot], aq = P.mi_a[slot];
-        const float3 org = f3(oq), wi = f3(dq), f = f3(aq), thr = f3(P.mi_t[slot]);
-        const float c1 = oq.w, ppdf = dq.w;
-        const Hit h = traverse<false, COUNT>(S, org, wi, 0.001f, 1e16f, nn, nt);
-        float4 Lq = P.L[slot];
-        float3 L = f3(Lq);
-        if (h.prim != 0xffffffffu) {
-            const float4 a3 = S.tri_attr[4 * (size_t)h.prim + 3];
-            const DevMaterial& m = S.materials[__float_as_uint(a3.w)];
-            if (m.is_light) {
-                const float4* Pp = S.tri_pos + 3 * (size_t)h.prim; const float4* A = S.tri_attr + 4 * (size_t)h.prim;
-                const float b0 = 1.0f - h.b1 - h.b2;
-                const float3 pos = b0 * f3(Pp[0]) + h.b1 * f3(Pp[1]) + h.b2 * f3(Pp[2]);
-                const float3 ln = normalize(b0 * f3(A[0]) + h.b1 * f3(A[1]) + h.b2 * f3(A[2]));
-                const float3 em = f3(m.emission[0], m.emission[1], m.emission[2]);
-                const float c2 = absdot(-wi, ln);
-                const float dist = length(pos - org);
-                const float invG = dist * dist / c2;
-                const float lpdf = (aq.w != 0.0f) ? 0.0f : light_pdf_area(S, h.prim) * invG;
-                const float w = ppdf / (ppdf + lpdf);
-                L += thr * w * c1 * em * f / ppdf;
+// MODE 0: extend (closest hit), 1: shadow (any hit), 2: MIS emitter ray (closest hit)
+// The warp runs in lock step through two kinds of phases: a NODE phase (every lane without pending triangles visits
+// one node) and a TRIANGLE phase, entered only when at least TRI_BATCH lanes have pending triangles (or no lane can
+// do node work): triangle tests are long and rare per node, so batching them across lanes is what keeps them from
+// running 3 lanes wide.
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace(DevScene S, FrameK F, WfPtrs P, int cur) {
+    __shared__ uint2 s_stack[(HJ_SSTACK ? HJ_SSTACK : 1) * HJ_TRACE_THREADS];
+    const uint32_t n = MODE == 0 ? P.cnt->n_extend[cur] : (MODE == 1 ? P.cnt->n_shadow : P.cnt->n_mis);
+    const uint32_t* __restrict__ queue = MODE == 0 ? P.q_ext[cur] : (MODE == 1 ? P.q_shadow : P.q_mis);
+    uint32_t* next = &P.cnt->next[MODE];
+    const uint32_t lane = threadIdx.x & 31u;
+    constexpr bool ANY = MODE == 1;
+    Trav t; t.sstack = s_stack + threadIdx.x;
+    bool active = false, exhausted = false;
+    uint32_t slot = 0, nn = 0, nt = 0, nr = 0, nn0 = 0, nt0 = 0;
+    while (true) {
+        const uint32_t idle = __ballot_sync(0xffffffffu, !active);
+        if (!exhausted && __popc(idle) >= REFILL_MIN) {
+            const int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(next, (uint32_t)__popc(idle));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!active) {
+                const uint32_t idx = base + __popc(idle & ((1u << lane) - 1u));
+                if (idx < n) {
+                    slot = queue[idx];
+                    if (slot != 0xffffffffu) {
+                        if (MODE == 0) { const float4 o = P.ray_o[slot], d = P.ray_d[slot]; t.init(f3(o), f3(d), 0.001f, 1e16f); }
+                        else if (MODE == 1) { const float4 o = P.sh_o[slot], d = P.sh_d[slot]; t.init(f3(o), f3(d), 0.001f, o.w); }
+                        else { const float4 o = P.mi_o[slot], d = P.mi_d[slot]; t.init(f3(o), f3(d), 0.001f, 1e16f); }
+                        active = true; nn0 = nn; nt0 = nt;
+                    }
+                }
             }
-        } else {
-            const float3 em = sky_radiance(S, wi, F.ibl);
-            L += thr * f * c1 * em / ppdf;
+            if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
         }
-        if (F.debug) { uint2 g = P.dbg[slot]; g.y = (g.y ^ (h.prim + 1u)) * 0x01000193u; P.dbg[slot] = g; }
-        P.L[slot] = f4(L, Lq.w + 1.0f);
-        nr++;
+        if (!__any_sync(0xffffffffu, active)) { if (exhausted) break; else continue; }
+#pragma unroll 1
+        for (int it = 0; it < TRACE_BURST; it++) {
+            // ---- node phase
+            bool done = false;
+            if (active && !t.has_tris()) {
+                if (t.fetch_group()) t.node_visit<COUNT>(S, nn);
+                else done = true;
+            }
+            // ---- triangle phase, batched
+            uint32_t tl = __ballot_sync(0xffffffffu, active && t.has_tris());
+            const uint32_t nl = __ballot_sync(0xffffffffu, active && !done && !t.has_tris());
+            if (tl && (__popc(tl) >= TRI_BATCH || nl == 0u)) {
+                const int keep = nl == 0u ? 1 : TRI_BATCH / 2;
+                do {
+                    if (active && t.has_tris()) { if (t.tri_one<ANY, COUNT>(S, nt)) { t.tg.y = 0u; t.ng.y = 0u; t.sp = 0; } }
+                    tl = __ballot_sync(0xffffffffu, active && t.has_tris());
+                } while (__popc(tl) >= keep);
+            }
+            if (done) {
+                if (MODE == 0) finish_extend(F, P, slot, t.best);
+                else if (MODE == 1) finish_shadow(P, slot, t.best);
+                else finish_mis(S, F, P, slot, t.best);
+                nr++; active = false;
+                if (COUNT) { atomicMax(&P.cnt->max_nodes, nn - nn0); atomicMax(&P.cnt->max_tris, nt - nt0); }
+            }
+        }
     }
-    warp_add64(&P.cnt->rays_extend, nr);
+    warp_add64(MODE == 1 ? &P.cnt->rays_shadow : &P.cnt->rays_extend, nr);
     if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
 }
 
 // ---------------------------------------------------------------------------------------------- accumulate / write-out
 __global__ void k_reset_queues(WfCounters* c, uint32_t n0, int all) {
     if (all) { c->n_extend[0] = n0; c->n_extend[1] = 0; }
-    c->n_shadow = 0; c->n_mis = 0;
+    c->n_shadow = 0; c->n_mis = 0; c->next[0] = c->next[1] = c->next[2] = 0;
 }
-__global__ void k_swap_queues(WfCounters* c, int cur) { c->n_extend[cur] = 0; c->n_shadow = 0; c->n_mis = 0; }
+__global__ void k_swap_queues(WfCounters* c, int cur) { c->n_extend[cur] = 0; c->n_shadow = 0; c->n_mis = 0; c->next[0] = c->next[1] = c->next[2] = 0; }
 
 // end of a pass: per pixel, add the pass's samples in sample order (same float addition order as the
 // reference's spp loop), and export the per-path debug records
@@ -376,8 +430,7 @@ int hj_trace_batch(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, u
 // ---------------------------------------------------------------------------------------------- host driver
 static inline uint32_t cdiv_u(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
 
-static int wf_reserve(hj_ctx* c, uint32_t cap, bool mis, bool debug) {
-    WavefrontState& w = c->wf;
+static int wf_reserve(hj_ctx* c, WavefrontState& w, uint32_t cap, bool mis, bool debug) {
     const size_t f4s = (size_t)cap * sizeof(float4);
     HJ_CUDA(c, w.ray_o.reserve(f4s)); HJ_CUDA(c, w.ray_d.reserve(f4s)); HJ_CUDA(c, w.hit.reserve(f4s));
     HJ_CUDA(c, w.thr.reserve(f4s)); HJ_CUDA(c, w.L.reserve(f4s)); HJ_CUDA(c, w.rng_depth.reserve((size_t)cap * 4));
@@ -387,8 +440,23 @@ static int wf_reserve(hj_ctx* c, uint32_t cap, bool mis, bool debug) {
     HJ_CUDA(c, w.sh_o.reserve(f4s)); HJ_CUDA(c, w.sh_d.reserve(f4s)); HJ_CUDA(c, w.sh_c.reserve(f4s));
     if (mis) { HJ_CUDA(c, w.mi_o.reserve(f4s)); HJ_CUDA(c, w.mi_d.reserve(f4s)); HJ_CUDA(c, w.mi_a.reserve(f4s)); HJ_CUDA(c, w.mi_t.reserve(f4s)); }
     HJ_CUDA(c, w.counters.reserve(sizeof(WfCounters)));
+    if (!w.stream) HJ_CUDA(c, cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
+    if (!w.ev_acc) HJ_CUDA(c, cudaEventCreateWithFlags(&w.ev_acc, cudaEventDisableTiming));
     w.capacity = cap;
     return HJ_OK;
+}
+
+static WfPtrs wf_ptrs(hj_ctx* c, WavefrontState& w) {
+    WfPtrs P;
+    P.ray_o = w.ray_o.as<float4>(); P.ray_d = w.ray_d.as<float4>(); P.hit = w.hit.as<float4>(); P.thr = w.thr.as<float4>();
+    P.L = w.L.as<float4>(); P.rng = w.rng_depth.as<uint32_t>(); P.dbg = w.dbg.as<uint2>();
+    P.q_ext[0] = w.q_extend[0].as<uint32_t>(); P.q_ext[1] = w.q_extend[1].as<uint32_t>();
+    P.q_shadow = w.q_shadow.as<uint32_t>(); P.q_mis = w.q_mis.as<uint32_t>();
+    P.sh_o = w.sh_o.as<float4>(); P.sh_d = w.sh_d.as<float4>(); P.sh_c = w.sh_c.as<float4>();
+    P.mi_o = w.mi_o.as<float4>(); P.mi_d = w.mi_d.as<float4>(); P.mi_a = w.mi_a.as<float4>(); P.mi_t = w.mi_t.as<float4>();
+    P.cnt = w.counters.as<WfCounters>();
+    P.aov_albedo = c->aov_albedo.as<float4>(); P.aov_normal = c->aov_normal.as<float4>();
+    return P;
 }
 
 int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
@@ -400,16 +468,22 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     if (fp->integrator < HJ_INTEGRATOR_PT || fp->integrator > HJ_INTEGRATOR_MIS) { c->err = "hj_render: unknown integrator"; return HJ_ERR_INVALID; }
     const uint32_t ns = fp->sample_end - fp->sample_begin;
     const bool debug = fp->debug_paths != 0;
-    // path slots per pass: whole samples of the whole frame
-    uint64_t target = c->opt_paths_per_pass > 0 ? (uint64_t)c->opt_paths_per_pass : (4ull << 20);
+    const bool timed = c->opt_time_stages != 0;
+    // passes: whole samples of the whole frame; `np` pipelines keep that many passes in flight (1 when timing stages)
+    int np = timed ? 1 : c->opt_pipelines;
+    uint64_t target = c->opt_paths_per_pass > 0 ? (uint64_t)c->opt_paths_per_pass : (2ull << 20);
     uint32_t spass = (uint32_t)(target / WH); if (spass < 1) spass = 1; if (spass > ns && ns) spass = ns;
     if (spass * WH > 0xfffffff0ull) spass = (uint32_t)(0xfffffff0ull / WH);
+    const uint32_t n_passes = ns ? (ns + spass - 1) / spass : 0;
+    if ((uint32_t)np > n_passes) np = (int)std::max(1u, n_passes);
     const uint32_t cap = (uint32_t)(spass * WH);
-    int rc = wf_reserve(c, cap, fp->integrator == HJ_INTEGRATOR_MIS, debug); if (rc) return rc;
+    for (int p = 0; p < np; p++) { int rc = wf_reserve(c, c->wf[p], cap, fp->integrator == HJ_INTEGRATOR_MIS, debug); if (rc) return rc; }
+    c->n_pipes_used = np;
     const size_t fb = (size_t)WH * sizeof(float4);
     HJ_CUDA(c, c->aov_color.reserve(fb)); HJ_CUDA(c, c->aov_albedo.reserve(fb)); HJ_CUDA(c, c->aov_normal.reserve(fb));
     HJ_CUDA(c, c->aov_accum.reserve(fb)); HJ_CUDA(c, c->aov_rgba8.reserve((size_t)WH * 4));
     if (debug) { HJ_CUDA(c, c->aov_path_rad.reserve((size_t)ns * fb)); HJ_CUDA(c, c->aov_path_ids.reserve((size_t)ns * WH * 8)); }
+    if (!c->ev_frame) HJ_CUDA(c, cudaEventCreateWithFlags(&c->ev_frame, cudaEventDisableTiming));
     cudaStream_t st = c->stream;
     if (c->fb_w != W || c->fb_h != H) {
         HJ_CUDA(c, cudaMemsetAsync(c->aov_albedo.p, 0, fb, st)); HJ_CUDA(c, cudaMemsetAsync(c->aov_normal.p, 0, fb, st));
@@ -423,75 +497,81 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     F.cright = make_float3(fp->camera_right[0], fp->camera_right[1], fp->camera_right[2]);
     F.cf = fp->camera_f; F.ibl = fp->ibl_intensity;
     F.integrator = fp->integrator; F.max_depth = fp->max_depth; F.tonemap = fp->tonemap; F.jitter = fp->pixel_jitter; F.debug = debug;
-    WavefrontState& w = c->wf;
-    WfPtrs P;
-    P.ray_o = w.ray_o.as<float4>(); P.ray_d = w.ray_d.as<float4>(); P.hit = w.hit.as<float4>(); P.thr = w.thr.as<float4>();
-    P.L = w.L.as<float4>(); P.rng = w.rng_depth.as<uint32_t>(); P.dbg = w.dbg.as<uint2>();
-    P.q_ext[0] = w.q_extend[0].as<uint32_t>(); P.q_ext[1] = w.q_extend[1].as<uint32_t>();
-    P.q_shadow = w.q_shadow.as<uint32_t>(); P.q_mis = w.q_mis.as<uint32_t>();
-    P.sh_o = w.sh_o.as<float4>(); P.sh_d = w.sh_d.as<float4>(); P.sh_c = w.sh_c.as<float4>();
-    P.mi_o = w.mi_o.as<float4>(); P.mi_d = w.mi_d.as<float4>(); P.mi_a = w.mi_a.as<float4>(); P.mi_t = w.mi_t.as<float4>();
-    P.cnt = w.counters.as<WfCounters>();
-    P.aov_albedo = c->aov_albedo.as<float4>(); P.aov_normal = c->aov_normal.as<float4>();
 
     int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
-    const uint32_t grid_cap = (uint32_t)sms * 16u;
-    const uint32_t grid = std::min(cdiv_u(cap, WF_THREADS), grid_cap);
+    const uint32_t grid = std::min(cdiv_u(cap, WF_THREADS), (uint32_t)sms * 16u);
+    // persistent traversal grid: exactly the blocks that are resident at once (a multiple of the SM count)
+    int occ = 8; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_trace<2, false>, HJ_TRACE_THREADS, 0);
+    if (c->opt_trace_blocks_per_sm > 0) occ = c->opt_trace_blocks_per_sm;
+    const uint32_t tgrid = std::min(cdiv_u(cap, HJ_TRACE_THREADS), (uint32_t)sms * (uint32_t)std::max(occ, 1));
     const bool count = c->opt_count_fetches != 0;
     uint64_t launches = 0;
 
-    const bool timed = c->opt_time_stages != 0;
     c->ev_kind.clear();
-    auto mark_begin = [&](int kind) {
+    auto mark_begin = [&](int kind, cudaStream_t s) {
         if (!timed) return;
         const size_t i = 2 * c->ev_kind.size();
         while (c->ev_pool.size() < i + 2) { cudaEvent_t e; cudaEventCreate(&e); c->ev_pool.push_back(e); }
         c->ev_kind.push_back(kind);
-        cudaEventRecord(c->ev_pool[i], st);
+        cudaEventRecord(c->ev_pool[i], s);
     };
-    auto mark_end = [&]() { if (timed) cudaEventRecord(c->ev_pool[2 * c->ev_kind.size() - 1], st); };
+    auto mark_end = [&](cudaStream_t s) { if (timed) cudaEventRecord(c->ev_pool[2 * c->ev_kind.size() - 1], s); };
+
     HJ_CUDA(c, cudaEventRecord(c->ev0, st));
-    HJ_CUDA(c, cudaMemsetAsync(w.counters.p, 0, sizeof(WfCounters), st));
     HJ_CUDA(c, cudaMemsetAsync(c->aov_accum.p, 0, fb, st));
-    for (uint32_t s0 = fp->sample_begin; s0 < fp->sample_end; s0 += spass) {
+    for (int p = 0; p < np; p++) HJ_CUDA(c, cudaMemsetAsync(c->wf[p].counters.p, 0, sizeof(WfCounters), st));
+    HJ_CUDA(c, cudaEventRecord(c->ev_frame, st));
+    for (int p = 0; p < np; p++) HJ_CUDA(c, cudaStreamWaitEvent(c->wf[p].stream, c->ev_frame, 0));
+    cudaEvent_t prev_acc = nullptr;
+    uint32_t pass = 0;
+    for (uint32_t s0 = fp->sample_begin; s0 < fp->sample_end; s0 += spass, pass++) {
+        WavefrontState& w = c->wf[pass % np];
+        cudaStream_t ps = w.stream;
+        const WfPtrs P = wf_ptrs(c, w);
         const uint32_t nsamp = std::min(spass, fp->sample_end - s0);
         const uint32_t nslots = (uint32_t)(nsamp * WH);
-        k_reset_queues<<<1, 1, 0, st>>>(P.cnt, nslots, 1);
-        k_raygen<<<grid, WF_THREADS, 0, st>>>(F, P, s0, nslots);
+        k_reset_queues<<<1, 1, 0, ps>>>(P.cnt, nslots, 1);
+        k_raygen<<<grid, WF_THREADS, 0, ps>>>(F, P, s0, nslots);
         launches += 2;
         int cur = 0;
         for (int depth = 0; depth < fp->max_depth; depth++) {
-            mark_begin(0);
-            if (count) k_extend<true><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur);
-            else k_extend<false><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur);
-            mark_end();
-            mark_begin(1);
-            if (fp->integrator == HJ_INTEGRATOR_PT) k_shade<HJ_INTEGRATOR_PT><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur, depth, s0);
-            else if (fp->integrator == HJ_INTEGRATOR_NEE) k_shade<HJ_INTEGRATOR_NEE><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur, depth, s0);
-            else k_shade<HJ_INTEGRATOR_MIS><<<grid, WF_THREADS, 0, st>>>(c->S, F, P, cur, depth, s0);
-            mark_end();
+            mark_begin(0, ps);
+            if (count) k_trace<0, true><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
+            else k_trace<0, false><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
+            mark_end(ps);
+            mark_begin(1, ps);
+            if (fp->integrator == HJ_INTEGRATOR_PT) k_shade<HJ_INTEGRATOR_PT><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+            else if (fp->integrator == HJ_INTEGRATOR_NEE) k_shade<HJ_INTEGRATOR_NEE><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+            else k_shade<HJ_INTEGRATOR_MIS><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+            mark_end(ps);
             launches += 2;
             if (fp->integrator != HJ_INTEGRATOR_PT) {
-                mark_begin(0);
-                if (count) k_shadow<true><<<grid, WF_THREADS, 0, st>>>(c->S, P);
-                else k_shadow<false><<<grid, WF_THREADS, 0, st>>>(c->S, P);
-                mark_end();
+                mark_begin(0, ps);
+                if (count) k_trace<1, true><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
+                else k_trace<1, false><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
+                mark_end(ps);
                 launches++;
             }
             if (fp->integrator == HJ_INTEGRATOR_MIS) {
-                mark_begin(0);
-                if (count) k_mis<true><<<grid, WF_THREADS, 0, st>>>(c->S, F, P);
-                else k_mis<false><<<grid, WF_THREADS, 0, st>>>(c->S, F, P);
-                mark_end();
+                mark_begin(0, ps);
+                if (count) k_trace<2, true><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
+                else k_trace<2, false><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
+                mark_end(ps);
                 launches++;
             }
-            k_swap_queues<<<1, 1, 0, st>>>(P.cnt, cur);
+            k_swap_queues<<<1, 1, 0, ps>>>(P.cnt, cur);
             launches++;
             cur ^= 1;
         }
-        k_accumulate<<<cdiv_u(WH, 256), 256, 0, st>>>(F, P, c->aov_accum.as<float4>(), s0, nsamp, c->aov_path_rad.as<float4>(), c->aov_path_ids.as<uint2>());
+        // accumulate in pass order: the float additions per pixel follow the sample order of the reference's spp loop
+        if (prev_acc) HJ_CUDA(c, cudaStreamWaitEvent(ps, prev_acc, 0));
+        k_accumulate<<<cdiv_u(WH, 256), 256, 0, ps>>>(F, P, c->aov_accum.as<float4>(), s0, nsamp, c->aov_path_rad.as<float4>(), c->aov_path_ids.as<uint2>());
+        HJ_CUDA(c, cudaEventRecord(w.ev_acc, ps));
+        prev_acc = w.ev_acc;
         launches++;
     }
+    // join: every pipeline's last accumulate precedes the finalize on the context stream
+    for (int p = 0; p < np; p++) { HJ_CUDA(c, cudaEventRecord(c->wf[p].ev_acc, c->wf[p].stream)); HJ_CUDA(c, cudaStreamWaitEvent(st, c->wf[p].ev_acc, 0)); }
     k_finalize<<<cdiv_u(WH, 256), 256, 0, st>>>(F, c->aov_accum.as<float4>(), c->aov_color.as<float4>(), c->aov_rgba8.as<uchar4>());
     launches++;
     HJ_CUDA(c, cudaEventRecord(c->ev1, st));
@@ -512,11 +592,16 @@ int hj_wavefront_finalize(hj_ctx* c) {
 
 // reads the device counters of the last frame into ctx->stats (after the stream has been synchronised)
 int hj_wavefront_stats(hj_ctx* c) {
-    if (!c->wf.counters.p) return HJ_OK;
-    WfCounters h;
-    HJ_CUDA(c, cudaMemcpy(&h, c->wf.counters.p, sizeof h, cudaMemcpyDeviceToHost));
-    c->stats.rays_extend = h.rays_extend; c->stats.rays_shadow = h.rays_shadow;
-    c->stats.nodes_fetched = h.nodes; c->stats.tris_fetched = h.tris;
+    WfCounters t{};
+    for (int p = 0; p < c->n_pipes_used; p++) {
+        WfCounters h;
+        HJ_CUDA(c, cudaMemcpy(&h, c->wf[p].counters.p, sizeof h, cudaMemcpyDeviceToHost));
+        t.rays_extend += h.rays_extend; t.rays_shadow += h.rays_shadow; t.nodes += h.nodes; t.tris += h.tris;
+        t.max_nodes = std::max(t.max_nodes, h.max_nodes); t.max_tris = std::max(t.max_tris, h.max_tris);
+    }
+    c->stats.rays_extend = t.rays_extend; c->stats.rays_shadow = t.rays_shadow;
+    c->stats.nodes_fetched = t.nodes; c->stats.tris_fetched = t.tris;
+    c->stats.max_nodes_per_ray = t.max_nodes; c->stats.max_tris_per_ray = t.max_tris;
     float ms = 0; if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->stats.ms_render = ms;
     double tt = 0, ts = 0;
     for (size_t i = 0; i < c->ev_kind.size(); i++) {

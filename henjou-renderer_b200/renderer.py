@@ -10,7 +10,7 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhenjou_b200.so")
+LIB_PATH = os.environ.get("HJ_LIB_PATH") or os.path.join(_HERE, "libhenjou_b200.so")   # HJ_LIB_PATH: kernel-tuning variants
 _lib = None
 
 

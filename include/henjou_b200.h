@@ -147,6 +147,10 @@ typedef struct hj_stats {
     float ms_accel;               /* device time of the last hj_accel_build                                     */
     uint32_t bvh_nodes;           /* nodes in the current acceleration structure                                */
     uint32_t bvh_node_bytes;      /* bytes per node                                                             */
+    uint32_t bvh_depth;           /* levels of the 8-wide tree                                                  */
+    uint32_t max_nodes_per_ray;   /* worst single ray of the last hj_render (only with "count_fetches")         */
+    uint32_t max_tris_per_ray;
+    uint32_t reserved;
 } hj_stats;
 
 int hj_abi_version(void);
@@ -157,7 +161,7 @@ int hj_create(hj_ctx** out, int device);
 void hj_destroy(hj_ctx* ctx);
 const char* hj_last_error(const hj_ctx* ctx);   /* ctx may be NULL: last hj_create error */
 
-/* "count_fetches" 0|1, "time_stages" 0|1, "paths_per_pass" N (0 = auto), "leaf_max" 1..4 (triangles per BVH leaf) */
+/* "count_fetches" 0|1, "time_stages" 0|1, "paths_per_pass" N (0 = auto), "leaf_max" 1..3 (triangles per BVH leaf) */
 int hj_set_option(hj_ctx* ctx, const char* key, int64_t value);
 
 /* ≙ Renderer::cpySceneDataToDevice + textureBind + setSky + setLUT (renderer.h:197-255, 740-898). */

@@ -32,7 +32,7 @@ def test_exports_match_header(lib):
 def test_struct_sizes():
     assert C.sizeof(abi.hj_material) == 25 * 4
     assert C.sizeof(abi.hj_frame_params) == 6 * 4 + 12 * 4 + 2 * 4 + 6 * 4
-    assert C.sizeof(abi.hj_stats) == 6 * 8 + 4 * 4 + 2 * 4
+    assert C.sizeof(abi.hj_stats) == 6 * 8 + 4 * 4 + 6 * 4
 
 
 def test_no_cpu_fallback(lib):
