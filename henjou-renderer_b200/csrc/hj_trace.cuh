@@ -82,7 +82,7 @@ struct Trav {
     RayPrep r; float tmin, tmax; Hit best;
     uint2 ng, tg; int sp; uint32_t oct_inv;
     uint2* sstack;                 // HJ_SSTACK entries in shared memory, strided by the block size (bank-conflict free)
-    uint2 stack[HJ_STACK];         // overflow beyond HJ_SSTACK: local memory
+    uint2* stack;                  // overflow beyond HJ_SSTACK: HJ_STACK entries of local memory (declared by the kernel)
     HJ_DI void push(const uint2 v) { if (sp < HJ_SSTACK) sstack[sp * HJ_TRACE_THREADS] = v; else stack[sp - HJ_SSTACK] = v; sp++; }
     HJ_DI uint2 pop() { sp--; return sp < HJ_SSTACK ? sstack[sp * HJ_TRACE_THREADS] : stack[sp - HJ_SSTACK]; }
 
@@ -130,6 +130,8 @@ struct Trav {
         const float tcur = (best.prim != 0xffffffffu) ? best.t : tmax;
         const bool nx = (r.oct & 1u) != 0, ny = (r.oct & 2u) != 0, nz = (r.oct & 4u) != 0;
         const uint32_t oct_inv4 = oct_inv * 0x01010101u;
+        uint32_t k4b;                                   // 2^23 as bits, kept opaque so that PRMT's selector is the immediate
+        asm("mov.b32 %0, 0x4B000000;" : "=r"(k4b));
         uint32_t hitmask = 0;
 #pragma unroll
         for (int h = 0; h < 2; h++) {
@@ -147,12 +149,12 @@ struct Trav {
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 const uint32_t sel = 0x7650u | (uint32_t)j;
-                const float tnx = __fmaf_rn(__uint_as_float(__byte_perm(nearx, 0x4B000000u, sel)), ax, oxn);
-                const float tny = __fmaf_rn(__uint_as_float(__byte_perm(neary, 0x4B000000u, sel)), ay, oyn);
-                const float tnz = __fmaf_rn(__uint_as_float(__byte_perm(nearz, 0x4B000000u, sel)), az, ozn);
-                const float tfx = __fmaf_rn(__uint_as_float(__byte_perm(farx, 0x4B000000u, sel)), ax, oxf);
-                const float tfy = __fmaf_rn(__uint_as_float(__byte_perm(fary, 0x4B000000u, sel)), ay, oyf);
-                const float tfz = __fmaf_rn(__uint_as_float(__byte_perm(farz, 0x4B000000u, sel)), az, ozf);
+                const float tnx = __fmaf_rn(__uint_as_float(__byte_perm(nearx, k4b, sel)), ax, oxn);
+                const float tny = __fmaf_rn(__uint_as_float(__byte_perm(neary, k4b, sel)), ay, oyn);
+                const float tnz = __fmaf_rn(__uint_as_float(__byte_perm(nearz, k4b, sel)), az, ozn);
+                const float tfx = __fmaf_rn(__uint_as_float(__byte_perm(farx, k4b, sel)), ax, oxf);
+                const float tfy = __fmaf_rn(__uint_as_float(__byte_perm(fary, k4b, sel)), ay, oyf);
+                const float tfz = __fmaf_rn(__uint_as_float(__byte_perm(farz, k4b, sel)), az, ozf);
                 const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
                 const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tcur));
                 const uint32_t bits = (child_bits4 >> (8 * j)) & 0xffu, idx = (bit_index4 >> (8 * j)) & 0xffu;
@@ -185,7 +187,8 @@ struct Trav {
 template <bool ANY, bool COUNT>
 HJ_DI Hit traverse(const DevScene& S, const float3& o, const float3& d, float tmin, float tmax, uint32_t& n_nodes, uint32_t& n_tris) {
     __shared__ uint2 s_stack[(HJ_SSTACK ? HJ_SSTACK : 1) * HJ_TRACE_THREADS];
-    Trav t; t.sstack = s_stack + threadIdx.x; t.init(o, d, tmin, tmax);
+    uint2 l_stack[HJ_STACK];
+    Trav t; t.sstack = s_stack + threadIdx.x; t.stack = l_stack; t.init(o, d, tmin, tmax);
     while (t.fetch_group()) {
         t.node_visit<COUNT>(S, n_nodes);
         while (t.has_tris()) if (t.tri_one<ANY, COUNT>(S, n_tris)) return t.best;

@@ -300,7 +300,8 @@ __global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace(DevScene S,
     uint32_t* next = &P.cnt->next[MODE];
     const uint32_t lane = threadIdx.x & 31u;
     constexpr bool ANY = MODE == 1;
-    Trav t; t.sstack = s_stack + threadIdx.x;
+    uint2 l_stack[HJ_STACK];
+    Trav t; t.sstack = s_stack + threadIdx.x; t.stack = l_stack;
     bool active = false, exhausted = false;
     uint32_t slot = 0, nn = 0, nt = 0, nr = 0, nn0 = 0, nt0 = 0;
     while (true) {
