@@ -62,7 +62,8 @@ void hj_destroy(hj_ctx* c) {
                       &c->d_xf, &c->d_inv_xf, &c->d_materials, &c->d_textures, &c->d_texels, &c->d_srgb, &c->d_light_ids, &c->d_light_em,
                       &c->d_ibl, &c->d_lut, &c->d_tri_pos, &c->d_tri_attr,
                       &c->bvh.keys, &c->bvh.keys_alt, &c->bvh.vals, &c->bvh.vals_alt, &c->bvh.block_hist, &c->bvh.blo, &c->bvh.bhi, &c->bvh.left,
-                      &c->bvh.right, &c->bvh.parent, &c->bvh.rfirst, &c->bvh.rlast, &c->bvh.flags, &c->bvh.bounds, &c->bvh.queue_a, &c->bvh.queue_b,
+                      &c->bvh.right, &c->bvh.parent, &c->bvh.cnt, &c->bvh.flags, &c->bvh.p_cid[0], &c->bvh.p_cid[1], &c->bvh.p_lo[0], &c->bvh.p_lo[1],
+                      &c->bvh.p_hi[0], &c->bvh.p_hi[1], &c->bvh.p_nn, &c->bvh.p_keep, &c->bvh.p_bcount, &c->bvh.bounds, &c->bvh.queue_a, &c->bvh.queue_b,
                       &c->bvh.counters, &c->bvh.nodes, &c->bvh.btris,
                       &c->aov_color, &c->aov_albedo, &c->aov_normal, &c->aov_rgba8, &c->aov_accum, &c->aov_path_rad, &c->aov_path_ids};
     for (DevBuf* b : bufs) b->release();
@@ -85,6 +86,7 @@ int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
     else if (!strcmp(key, "paths_per_pass")) c->opt_paths_per_pass = value;
     else if (!strcmp(key, "trace_blocks_per_sm")) { HJ_REQUIRE(c, value >= 0 && value <= 32, HJ_ERR_INVALID, "hj_set_option: trace_blocks_per_sm must be 0 (auto) .. 32"); c->opt_trace_blocks_per_sm = (int)value; }
     else if (!strcmp(key, "pipelines")) { HJ_REQUIRE(c, value >= 1 && value <= HJ_MAX_PIPES, HJ_ERR_INVALID, "hj_set_option: pipelines must be 1..8"); c->opt_pipelines = (int)value; }
+    else if (!strcmp(key, "builder")) { HJ_REQUIRE(c, value == 0 || value == 1, HJ_ERR_INVALID, "hj_set_option: builder must be 0 (LBVH) or 1 (PLOC)"); c->opt_builder = (int)value; c->bvh.have_topology = false; }
     else if (!strcmp(key, "leaf_max")) { HJ_REQUIRE(c, value >= 1 && value <= 3, HJ_ERR_INVALID, "hj_set_option: leaf_max must be 1..3"); c->opt_leaf_max = (int)value; }
     else { c->err = std::string("hj_set_option: unknown option '") + key + "'"; return HJ_ERR_INVALID; }
     return HJ_OK;

@@ -173,7 +173,7 @@ HJ_DI int delta(const uint64_t* __restrict__ k, int n, int i, int j) {
 }
 
 // internal node i in [0,N-1); node ids: internal i -> i, leaf j -> N-1+j
-__global__ void k_karras(const uint64_t* __restrict__ keys, int n, uint32_t* left, uint32_t* right, uint32_t* parent, uint32_t* rfirst, uint32_t* rlast) {
+__global__ void k_karras(const uint64_t* __restrict__ keys, int n, uint32_t* left, uint32_t* right, uint32_t* parent, uint32_t* cnt) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
     const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
@@ -194,7 +194,7 @@ __global__ void k_karras(const uint64_t* __restrict__ keys, int n, uint32_t* lef
     const uint32_t L = (lo == gamma) ? (uint32_t)(n - 1 + gamma) : (uint32_t)gamma;
     const uint32_t R = (hi == gamma + 1) ? (uint32_t)(n - 1 + gamma + 1) : (uint32_t)(gamma + 1);
     left[i] = L; right[i] = R; parent[L] = (uint32_t)i; parent[R] = (uint32_t)i;
-    rfirst[i] = (uint32_t)lo; rlast[i] = (uint32_t)hi;
+    cnt[i] = (uint32_t)(hi - lo + 1);
     if (i == 0) parent[0] = 0xffffffffu;
 }
 
@@ -222,18 +222,120 @@ __global__ void k_fit(const DevScene S, const uint32_t* __restrict__ sorted, int
     }
 }
 
+// ---------------------------------------------------------------------------------------------- PLOC
+// Parallel locally-ordered clustering (Meister & Bittner 2018): bottom-up agglomeration of the Morton-ordered
+// clusters. Every round each cluster looks PLOC_RADIUS neighbours to either side for the partner that minimises the
+// surface area of the merged box; mutual nearest neighbours merge. Builds a much better tree than the Karras radix
+// tree over the same order (fewer node visits per ray, no pathological long rays through flat tessellated surfaces).
+#define PLOC_RADIUS 12
+#define PLOC_THREADS 256
+
+__global__ void k_ploc_init(const DevScene S, const uint32_t* __restrict__ sorted, int n, uint32_t* cid, float4* clo, float4* chi, float4* blo, float4* bhi) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const float4* P = S.tri_pos + 3 * (size_t)sorted[j];
+    const float3 a = f3(P[0]), b = f3(P[1]), c = f3(P[2]);
+    const float4 lo = make_float4(fminf(a.x, fminf(b.x, c.x)), fminf(a.y, fminf(b.y, c.y)), fminf(a.z, fminf(b.z, c.z)), 0.0f);
+    const float4 hi = make_float4(fmaxf(a.x, fmaxf(b.x, c.x)), fmaxf(a.y, fmaxf(b.y, c.y)), fmaxf(a.z, fmaxf(b.z, c.z)), 0.0f);
+    const uint32_t id = (uint32_t)(n - 1 + j);
+    cid[j] = id; clo[j] = lo; chi[j] = hi; blo[id] = lo; bhi[id] = hi;
+}
+
+HJ_DI float merged_area(const float4& alo, const float4& ahi, const float4& blo, const float4& bhi) {
+    const float dx = fmaxf(ahi.x, bhi.x) - fminf(alo.x, blo.x), dy = fmaxf(ahi.y, bhi.y) - fminf(alo.y, blo.y),
+                dz = fmaxf(ahi.z, bhi.z) - fminf(alo.z, blo.z);
+    return dx * dy + dy * dz + dz * dx;
+}
+
+// nearest neighbour inside the window; ties resolved by the (min index, max index) pair so that "nearest" is a strict
+// total order on pairs and the globally closest pair is always mutual (guarantees progress)
+__global__ void __launch_bounds__(PLOC_THREADS) k_ploc_nn(int n, const float4* __restrict__ clo, const float4* __restrict__ chi, uint32_t* __restrict__ nn) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 lo = clo[i], hi = chi[i];
+    float best = FLT_MAX; int bj = -1;
+    const int j0 = max(0, i - PLOC_RADIUS), j1 = min(n - 1, i + PLOC_RADIUS);
+    for (int j = j0; j <= j1; j++) {
+        if (j == i) continue;
+        const float d = merged_area(lo, hi, clo[j], chi[j]);
+        bool better = d < best;
+        if (d == best && bj >= 0) {
+            const int a0 = min(i, j), a1 = max(i, j), b0 = min(i, bj), b1 = max(i, bj);
+            better = a0 < b0 || (a0 == b0 && a1 < b1);
+        }
+        if (better) { best = d; bj = j; }
+    }
+    nn[i] = (uint32_t)bj;
+}
+
+__global__ void __launch_bounds__(PLOC_THREADS) k_ploc_merge(int n, int n_leaves, uint32_t* cid, float4* clo, float4* chi, const uint32_t* __restrict__ nn,
+                                                               uint32_t* node_ctr, uint32_t* left, uint32_t* right, uint32_t* parent, uint32_t* cnt,
+                                                               float4* blo, float4* bhi, uint32_t* keep, uint32_t* block_count) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int k = 0;
+    if (i < n) {
+        const int j = (int)nn[i];
+        const bool mutual = j >= 0 && (int)nn[j] == i;
+        k = 1;
+        if (mutual) {
+            if (i < j) {
+                const uint32_t id = atomicAdd(node_ctr, 1u);
+                const uint32_t a = cid[i], b = cid[j];
+                const float4 alo = clo[i], ahi = chi[i], xlo = clo[j], xhi = chi[j];
+                const float4 lo = make_float4(fminf(alo.x, xlo.x), fminf(alo.y, xlo.y), fminf(alo.z, xlo.z), 0.0f);
+                const float4 hi = make_float4(fmaxf(ahi.x, xhi.x), fmaxf(ahi.y, xhi.y), fmaxf(ahi.z, xhi.z), 0.0f);
+                left[id] = a; right[id] = b; parent[a] = id; parent[b] = id;
+                cnt[id] = (a >= (uint32_t)(n_leaves - 1) ? 1u : cnt[a]) + (b >= (uint32_t)(n_leaves - 1) ? 1u : cnt[b]);
+                blo[id] = lo; bhi[id] = hi;
+                cid[i] = id; clo[i] = lo; chi[i] = hi;
+            } else k = 0;
+        }
+        keep[i] = (uint32_t)k;
+    }
+    const int total = __syncthreads_count(k);
+    if (threadIdx.x == 0) block_count[blockIdx.x] = (uint32_t)total;
+}
+
+__global__ void __launch_bounds__(PLOC_THREADS) k_ploc_compact(int n, const uint32_t* __restrict__ keep, const uint32_t* __restrict__ block_off,
+                                                                 const uint32_t* __restrict__ cid, const float4* __restrict__ clo, const float4* __restrict__ chi,
+                                                                 uint32_t* __restrict__ cid2, float4* __restrict__ clo2, float4* __restrict__ chi2) {
+    __shared__ uint32_t wsum[PLOC_THREADS / 32];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool k = i < n && keep[i] != 0u;
+    const uint32_t m = __ballot_sync(0xffffffffu, k);
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) wsum[w] = __popc(m);
+    __syncthreads();
+    uint32_t base = block_off[blockIdx.x];
+    for (int ww = 0; ww < w; ww++) base += wsum[ww];
+    if (k) {
+        const uint32_t pos = base + __popc(m & ((1u << lane) - 1u));
+        cid2[pos] = cid[i]; clo2[pos] = clo[i]; chi2[pos] = chi[i];
+    }
+}
+
 // ---------------------------------------------------------------------------------------------- collapse to 8-wide
 struct CollapseArgs {
     int n; uint32_t leaf_max;
-    const uint32_t *left, *right, *rfirst, *rlast, *sorted;
+    const uint32_t *left, *right, *cnt, *sorted;
     const float4 *blo, *bhi;
     const float4* tri_pos;
     uint4* nodes; float4* btris;
     uint32_t* counters;     // [0] nodes allocated, [1] triangles allocated, [2] next-level queue length
 };
 
-HJ_DI uint32_t bn_count(const CollapseArgs& a, uint32_t id) { return id >= (uint32_t)(a.n - 1) ? 1u : a.rlast[id] - a.rfirst[id] + 1u; }
-HJ_DI uint32_t bn_first(const CollapseArgs& a, uint32_t id) { return id >= (uint32_t)(a.n - 1) ? id - (uint32_t)(a.n - 1) : a.rfirst[id]; }
+HJ_DI uint32_t bn_count(const CollapseArgs& a, uint32_t id) { return id >= (uint32_t)(a.n - 1) ? 1u : a.cnt[id]; }
+// the (<= 3) leaves below a binary node, as indices into the Morton-sorted triangle order
+HJ_DI int bn_leaves(const CollapseArgs& a, uint32_t id, uint32_t out[4]) {
+    uint32_t st[4]; int sp = 0, n = 0;
+    st[sp++] = id;
+    while (sp) {
+        const uint32_t x = st[--sp];
+        if (x >= (uint32_t)(a.n - 1)) { if (n < 4) out[n++] = x - (uint32_t)(a.n - 1); }
+        else { st[sp++] = a.right[x]; st[sp++] = a.left[x]; }
+    }
+    return n;
+}
 HJ_DI float bn_area(const CollapseArgs& a, uint32_t id) {
     const float4 l = a.blo[id], h = a.bhi[id];
     const float dx = h.x - l.x, dy = h.y - l.y, dz = h.z - l.z;
@@ -340,9 +442,10 @@ __global__ void k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32
         if (k < 0) continue;
         if (imask & (1u << s)) { qout[qbase + r] = make_uint2(ch[k], child_base + r); r++; }
         else {
-            const uint32_t first = bn_first(a, ch[k]), cnt = bn_count(a, ch[k]), off = meta[s] & 31u;
+            uint32_t lv[4];
+            const uint32_t cnt = (uint32_t)bn_leaves(a, ch[k], lv), off = meta[s] & 31u;
             for (uint32_t j = 0; j < cnt; j++) {
-                const uint32_t prim = a.sorted[first + j];
+                const uint32_t prim = a.sorted[lv[j]];
                 const float4* P = a.tri_pos + 3 * (size_t)prim;
                 float4* T = a.btris + 3 * (size_t)(tri_base + off + j);
                 float4 v0 = P[0]; v0.w = __uint_as_float(prim);
@@ -375,7 +478,6 @@ int hj_bvh_build(hj_ctx* c, int mode) {
         HJ_CUDA(c, B.block_hist.reserve((size_t)256 * nb * 4));
         HJ_CUDA(c, B.left.reserve((size_t)n * 4)); HJ_CUDA(c, B.right.reserve((size_t)n * 4));
         HJ_CUDA(c, B.parent.reserve(2 * (size_t)n * 4));
-        HJ_CUDA(c, B.rfirst.reserve((size_t)n * 4)); HJ_CUDA(c, B.rlast.reserve((size_t)n * 4));
         k_morton<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.bounds.as<int>(), B.keys.as<uint64_t>(), B.vals.as<uint32_t>());
         uint64_t *k0 = B.keys.as<uint64_t>(), *k1 = B.keys_alt.as<uint64_t>();
         uint32_t *v0 = B.vals.as<uint32_t>(), *v1 = B.vals_alt.as<uint32_t>();
@@ -385,14 +487,48 @@ int hj_bvh_build(hj_ctx* c, int mode) {
             k_rs_scatter<<<nb, RS_THREADS, 0, st>>>(k0, v0, n, 8 * pass, B.block_hist.as<uint32_t>(), nb, k1, v1);
             std::swap(k0, k1); std::swap(v0, v1);
         }
-        if (n > 1)
+        HJ_CUDA(c, B.cnt.reserve((size_t)n * 4));
+        HJ_CUDA(c, B.blo.reserve(2 * (size_t)n * sizeof(float4))); HJ_CUDA(c, B.bhi.reserve(2 * (size_t)n * sizeof(float4)));
+        B.root = 0;
+        if (n > 1 && c->opt_builder == 0) {
             k_karras<<<cdiv(n - 1, 256), 256, 0, st>>>(B.keys.as<uint64_t>(), (int)n, B.left.as<uint32_t>(), B.right.as<uint32_t>(),
-                                                       B.parent.as<uint32_t>(), B.rfirst.as<uint32_t>(), B.rlast.as<uint32_t>());
+                                                       B.parent.as<uint32_t>(), B.cnt.as<uint32_t>());
+        } else if (n > 1) {
+            const uint32_t nbmax = cdiv(n, PLOC_THREADS);
+            HJ_CUDA(c, B.p_cid[0].reserve((size_t)n * 4)); HJ_CUDA(c, B.p_cid[1].reserve((size_t)n * 4));
+            for (int k = 0; k < 2; k++) { HJ_CUDA(c, B.p_lo[k].reserve((size_t)n * 16)); HJ_CUDA(c, B.p_hi[k].reserve((size_t)n * 16)); }
+            HJ_CUDA(c, B.p_nn.reserve((size_t)n * 4)); HJ_CUDA(c, B.p_keep.reserve((size_t)n * 4));
+            HJ_CUDA(c, B.p_bcount.reserve(((size_t)nbmax + 1) * 4)); HJ_CUDA(c, B.counters.reserve(4 * sizeof(uint32_t)));
+            HJ_CUDA(c, cudaMemsetAsync(B.counters.p, 0, 16, st));
+            k_ploc_init<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.vals.as<uint32_t>(), (int)n, B.p_cid[0].as<uint32_t>(), B.p_lo[0].as<float4>(), B.p_hi[0].as<float4>(),
+                                                      B.blo.as<float4>(), B.bhi.as<float4>());
+            uint32_t cur_n = n; int pp = 0, rounds = 0;
+            while (cur_n > 1) {
+                const uint32_t nb = cdiv(cur_n, PLOC_THREADS);
+                k_ploc_nn<<<nb, PLOC_THREADS, 0, st>>>((int)cur_n, B.p_lo[pp].as<float4>(), B.p_hi[pp].as<float4>(), B.p_nn.as<uint32_t>());
+                k_ploc_merge<<<nb, PLOC_THREADS, 0, st>>>((int)cur_n, (int)n, B.p_cid[pp].as<uint32_t>(), B.p_lo[pp].as<float4>(), B.p_hi[pp].as<float4>(), B.p_nn.as<uint32_t>(),
+                                                          B.counters.as<uint32_t>(), B.left.as<uint32_t>(), B.right.as<uint32_t>(), B.parent.as<uint32_t>(), B.cnt.as<uint32_t>(),
+                                                          B.blo.as<float4>(), B.bhi.as<float4>(), B.p_keep.as<uint32_t>(), B.p_bcount.as<uint32_t>());
+                HJ_CUDA(c, cudaMemsetAsync(B.p_bcount.as<uint32_t>() + nb, 0, 4, st));
+                k_rs_scan<<<1, 1024, 0, st>>>(B.p_bcount.as<uint32_t>(), nb + 1);
+                k_ploc_compact<<<nb, PLOC_THREADS, 0, st>>>((int)cur_n, B.p_keep.as<uint32_t>(), B.p_bcount.as<uint32_t>(), B.p_cid[pp].as<uint32_t>(), B.p_lo[pp].as<float4>(),
+                                                            B.p_hi[pp].as<float4>(), B.p_cid[pp ^ 1].as<uint32_t>(), B.p_lo[pp ^ 1].as<float4>(), B.p_hi[pp ^ 1].as<float4>());
+                uint32_t next_n = 0;
+                HJ_CUDA(c, cudaMemcpyAsync(&next_n, B.p_bcount.as<uint32_t>() + nb, 4, cudaMemcpyDeviceToHost, st));
+                HJ_CUDA(c, cudaStreamSynchronize(st));
+                if (next_n >= cur_n || next_n == 0 || ++rounds > 4096) { c->err = "hj_accel_build: PLOC made no progress"; return HJ_ERR_INVALID; }
+                cur_n = next_n; pp ^= 1;
+            }
+            B.root = n - 2;      // the last merge allocated the last internal id
+            const uint32_t none = 0xffffffffu;
+            HJ_CUDA(c, cudaMemcpyAsync(B.parent.as<uint32_t>() + B.root, &none, 4, cudaMemcpyHostToDevice, st));
+            B.ploc_rounds = rounds;
+        }
         B.have_topology = true;
     }
-    HJ_CUDA(c, B.blo.reserve(2 * (size_t)n * sizeof(float4))); HJ_CUDA(c, B.bhi.reserve(2 * (size_t)n * sizeof(float4)));
     HJ_CUDA(c, B.flags.reserve((size_t)n * 4));
     HJ_CUDA(c, cudaMemsetAsync(B.flags.p, 0, (size_t)n * 4, st));
+    if (!topo || c->opt_builder == 0 || n == 1)     // PLOC computes the boxes while it merges; a refit recomputes them bottom-up
     k_fit<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.vals.as<uint32_t>(), (int)n, B.left.as<uint32_t>(), B.right.as<uint32_t>(), B.parent.as<uint32_t>(),
                                         B.flags.as<uint32_t>(), B.blo.as<float4>(), B.bhi.as<float4>());
     // collapse, level by level
@@ -400,12 +536,12 @@ int hj_bvh_build(hj_ctx* c, int mode) {
     HJ_CUDA(c, B.queue_a.reserve((size_t)n * sizeof(uint2))); HJ_CUDA(c, B.queue_b.reserve((size_t)n * sizeof(uint2)));
     HJ_CUDA(c, B.counters.reserve(4 * sizeof(uint32_t)));
     const uint32_t init_counters[4] = {1u, 0u, 0u, 0u};
-    const uint2 root = make_uint2(0u, 0u);
+    const uint2 root = make_uint2(B.root, 0u);
     HJ_CUDA(c, cudaMemcpyAsync(B.counters.p, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, st));
     HJ_CUDA(c, cudaMemcpyAsync(B.queue_a.p, &root, sizeof root, cudaMemcpyHostToDevice, st));
     CollapseArgs a;
     a.n = (int)n; a.leaf_max = (uint32_t)c->opt_leaf_max;
-    a.left = B.left.as<uint32_t>(); a.right = B.right.as<uint32_t>(); a.rfirst = B.rfirst.as<uint32_t>(); a.rlast = B.rlast.as<uint32_t>();
+    a.left = B.left.as<uint32_t>(); a.right = B.right.as<uint32_t>(); a.cnt = B.cnt.as<uint32_t>();
     a.sorted = B.vals.as<uint32_t>(); a.blo = B.blo.as<float4>(); a.bhi = B.bhi.as<float4>(); a.tri_pos = c->S.tri_pos;
     a.nodes = B.nodes.as<uint4>(); a.btris = B.btris.as<float4>(); a.counters = B.counters.as<uint32_t>();
     uint2 *qi = B.queue_a.as<uint2>(), *qo = B.queue_b.as<uint2>();

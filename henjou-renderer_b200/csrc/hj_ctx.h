@@ -29,7 +29,9 @@ struct BvhState {
     DevBuf keys, keys_alt, vals, vals_alt, block_hist;
     DevBuf blo, bhi;              // float4[2N-1] boxes: internal i -> i, leaf j -> N-1+j
     DevBuf left, right, parent;   // uint32
-    DevBuf rfirst, rlast, flags;  // uint32[N-1]
+    DevBuf cnt, flags;            // uint32[N-1]: leaves below an internal node; fit counters
+    DevBuf p_cid[2], p_lo[2], p_hi[2], p_nn, p_keep, p_bcount;   // PLOC cluster arrays (ping-pong)
+    uint32_t root = 0; int ploc_rounds = 0;
     DevBuf bounds;                // 6 ordered-int atomics
     DevBuf queue_a, queue_b, counters;   // collapse work queues: uint2 {binary node, wide node}
     DevBuf nodes, btris;          // the traversal structure
@@ -60,7 +62,7 @@ struct hj_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;
     // options
-    int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3, opt_trace_blocks_per_sm = 0, opt_pipelines = 8;
+    int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3, opt_trace_blocks_per_sm = 0, opt_pipelines = 8, opt_builder = 0;   // builder: 0 Karras radix tree (LBVH), 1 PLOC
     int64_t opt_paths_per_pass = 0;
     // scene
     bool have_scene = false, have_accel = false, have_frame = false;
