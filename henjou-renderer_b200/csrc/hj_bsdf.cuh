@@ -82,7 +82,7 @@ struct Disney {
         return 0.25f * d * g * f / (fabsf(wo.y) * fabsf(wi.y));
     }
     // :179-235
-    HJ_DI float3 eval(const DevScene& S, const float3& wo, const float3& wi) const {
+    HJ_NI float3 eval(const DevScene& S, const float3& wo, const float3& wi) const {
         float3 wm = normalize(wo + wi);
         float dot_wi_n = fabsf(wi.y);
         float dot_wo_n = fabsf(wi.y);               // sic (:189)
@@ -105,7 +105,7 @@ struct Disney {
         return (lerp3(f_diffuse, f_ss, subsurface) + f_sheen) * (1.0f - metallic) + f_spec + f_cc * clearcoat;
     }
     // :237-307 — two RNG calls: lobe select, then the 2-D sample
-    HJ_DI float3 sample(const DevScene& S, const float3& wo, float3& wi, float& pdf, Sampler& st) const {
+    HJ_NI float3 sample(const DevScene& S, const float3& wo, float3& wi, float& pdf, Sampler& st) const {
         float dwt = 1.0f * (1.0f - metallic), swt = 0.5f, cwt = 0.0f;
         float sum = dwt + swt + cwt;
         float dw = dwt / sum, sw = swt / sum, cw = cwt / sum;
@@ -216,7 +216,7 @@ struct MultiScatterGGX {
         return wo;
     }
     // :784-819. `wo` is left untouched on the NaN exit (the reference leaves it unset): callers pre-set (0,1,0).
-    HJ_DI float3 walk(const float3& wi, float3& wo, int& order, Sampler& st) const {
+    HJ_NI float3 walk(const float3& wi, float3& wo, int& order, Sampler& st) const {
         float3 wr = -wi;
         float hr = 1.0f + invC1(0.999f);
         order = 0;

@@ -71,7 +71,7 @@ HJ_DI float2 cmj_point(uint32_t index, uint32_t scramble) {
     return make_float2((index % 4 + (sy + jx) / 4) / 4, (index / 4 + (sx + jy) / 4) / 4);
 }
 // cmj.h:119-128: one call = one dimension
-HJ_DI float2 draw2(Sampler& s) {
+static HJ_NI float2 draw2(Sampler& s) {
     const uint32_t index = s.n_spp % 16u;
     const uint32_t scr = xxhash32_u4(s.n_spp / 16u, s.image_idx, s.depth, s.scramble);
     const float2 r = cmj_point(index, scr);

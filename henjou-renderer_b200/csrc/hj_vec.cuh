@@ -10,6 +10,7 @@
 #include <stdint.h>
 
 #define HJ_DI __device__ __forceinline__
+#define HJ_NI __device__ __noinline__     // big shading routines: one copy each keeps k_shade inside the instruction cache
 
 #ifndef M_PIf
 #define M_PIf 3.14159265358979323846f
