@@ -37,7 +37,7 @@ struct Disney {
         float phi = 2.0f * HJ_PI * uv.x;
         float z = fmaf((1.0f - uv.y), (1.0f + swo.y), -swo.y);
         float st = sqrtf(clampf(1.0f - z * z, 0.0f, 1.0f));
-        float x = st * cosf(phi), y = st * sinf(phi);
+        float x = st * hj_cosf(phi), y = st * hj_sinf(phi);
         float3 h = f3(x, z, y) + swo;
         return normalize(f3(h.x * alpha, h.y, h.z * alpha));
     }
@@ -57,10 +57,10 @@ struct Disney {
         return cc_D(wm, cc_alpha) * fabsf(wm.y) / (4.0f * fabsf(dot(wm, wo)));
     }
     HJ_DI float3 sample_clearcoat(const float2& uv, const float3& wo, float& pdf) const {           // :93-100
-        float ct = sqrtf(fmaxf((1.0f - powf(cc_alpha * cc_alpha, 1.0f - uv.x)) / (1.0f - cc_alpha * cc_alpha), 0.0f));
+        float ct = sqrtf(fmaxf((1.0f - hj_powf(cc_alpha * cc_alpha, 1.0f - uv.x)) / (1.0f - cc_alpha * cc_alpha), 0.0f));
         float st = sqrtf(fmaxf(1.0f - ct * ct, 0.0f));
         float phi = HJ_TWO_PI * uv.y;
-        float3 wm = f3(cosf(phi) * st, ct, sinf(phi) * st);
+        float3 wm = f3(hj_cosf(phi) * st, ct, hj_sinf(phi) * st);
         pdf = pdf_clearcoat(wm, wo);
         return wm;
     }
@@ -113,10 +113,10 @@ struct Disney {
         float pd = 1.0f, ps = 1.0f, pc = 1.0f;
         float2 xi = draw2(st);
         if (sel < dw) {
-            float theta = 0.5f * acosf(1.0f - 2.0f * xi.x);    // sampleDiffuse :30-38
+            float theta = 0.5f * hj_acosf(1.0f - 2.0f * xi.x);    // sampleDiffuse :30-38
             float phi = 2.0f * M_PIf * xi.y;
-            float ct = cosf(theta), sn = sinf(theta);
-            wi = f3(cosf(phi) * sn, ct, sinf(phi) * sn);
+            float ct = hj_cosf(theta), sn = hj_sinf(theta);
+            wi = f3(hj_cosf(phi) * sn, ct, hj_sinf(phi) * sn);
             pd = pdf_diffuse(wi);
             float3 wm = normalize(wi + wo);
             ps = pdf_specular(wm, wo);
@@ -189,7 +189,7 @@ struct MultiScatterGGX {
     HJ_DI float G1_height(const float3& w, float h0) const {                                                      // :551-563
         if (w.y > 0.9999f) return 1.0f;
         if (w.y <= 0.0f) return 0.0f;
-        return powf(C1(h0), Lambda(w));
+        return hj_powf(C1(h0), Lambda(w));
     }
     HJ_DI float sample_height(const float3& wr, float hr, float U) const {                                        // :566-586
         if (wr.y > 0.9999f) return FLT_MAX;
@@ -197,14 +197,14 @@ struct MultiScatterGGX {
         if (fabsf(wr.y) < 0.0001f) return hr;
         const float g = G1_height(wr, hr);
         if (U > 1.0f - g) return FLT_MAX;
-        return invC1(C1(hr) / powf((1.0f - U), 1.0f / Lambda(wr)));
+        return invC1(C1(hr) / hj_powf((1.0f - U), 1.0f / Lambda(wr)));
     }
     HJ_DI float3 sample_vndf(const float2& uv, const float3& wo) const {                                          // :616-632
         float3 swo = normalize(f3(wo.x * alpha, wo.y, wo.z * alpha));
         float phi = 2.0f * HJ_PI * uv.x;
         float z = fmaf((1.0f - uv.y), (1.0f + swo.y), -swo.y);
         float st = sqrtf(clampf(1.0f - z * z, 0.0f, 1.0f));
-        float x = st * cosf(phi), y = st * sinf(phi);
+        float x = st * hj_cosf(phi), y = st * hj_sinf(phi);
         float3 h = f3(x, z, y) + swo;
         return normalize(f3(h.x * alpha, h.y, h.z * alpha));
     }

@@ -10,6 +10,13 @@
 #define HJ_TWO_PI 6.28318530717958647692f   // common/constant.h:4
 #define HJ_INV_PI 0.31830988618379067154f   // common/constant.h:6
 
+// One copy of each libm routine the shading code calls (they inline to 50-200 instructions apiece; k_shade calls them
+// from ~40 sites and must stay inside the instruction cache). Same functions, same results.
+static HJ_NI float hj_powf(float a, float b) { return powf(a, b); }
+static HJ_NI float hj_sinf(float a) { return sinf(a); }
+static HJ_NI float hj_cosf(float a) { return cosf(a); }
+static HJ_NI float hj_acosf(float a) { return acosf(a); }
+
 // cmj.h:38-51 xxhash32(uint4)
 HJ_DI uint32_t xxhash32_u4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
     const uint32_t P2 = 2246822519u, P3 = 3266489917u, P4 = 668265263u, P5 = 374761393u;
@@ -85,14 +92,14 @@ HJ_DI float draw1(Sampler& s) { return draw2(s).x; }
 // math.h:26-29
 HJ_DI float3 schlick3(const float3& F0, const float3& w, const float3& n) {
     float term1 = 1.0f - dot(w, n);
-    return (1.0f - F0) * powf(term1, 5.0f) + F0;
+    return (1.0f - F0) * hj_powf(term1, 5.0f) + F0;
 }
 // math.h:31-37
 HJ_DI float schlick_ior(float no, float ni, const float3& w, const float3& n) {
     float F0 = (no - ni) / (no + ni);
     F0 = F0 * F0;
     float term1 = 1.0f - dot(w, n);
-    return F0 + (1.0f - F0) * powf(term1, 5.0f);
+    return F0 + (1.0f - F0) * hj_powf(term1, 5.0f);
 }
 // math.h:43-51
 HJ_DI void onb(const float3& n, float3& t, float3& b) {

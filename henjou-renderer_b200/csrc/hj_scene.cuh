@@ -60,7 +60,7 @@ HJ_DI float4 texel8(const DevTexture& im, const float* srgb_table, int x, int y)
     return make_float4(p.x / 255.0f, p.y / 255.0f, p.z / 255.0f, p.w / 255.0f);
 }
 // CUDA linear filtering with normalised coords: xB = u*W - 0.5, i = floor(xB), a = frac(xB)
-HJ_DI float4 bilinear8(const DevTexture& im, const float* srgb_table, float u, float v) {
+static HJ_NI float4 bilinear8(const DevTexture& im, const float* srgb_table, float u, float v) {
     float xb = u * (float)im.w - 0.5f, yb = v * (float)im.h - 0.5f;
     float fx = floorf(xb), fy = floorf(yb);
     float a = xb - fx, b = yb - fy;
@@ -73,7 +73,7 @@ HJ_DI float4 bilinear8(const DevTexture& im, const float* srgb_table, float u, f
 HJ_DI float4 texelF(const DevScene& S, int x, int y) { return S.ibl[(size_t)wrapi(y, S.ibl_h) * S.ibl_w + wrapi(x, S.ibl_w)]; }
 
 // D6: equirect sky lookup, y-up: u = phi/2pi with phi = atan2(z,x) in [0,2pi), v = acos(y)/pi.
-HJ_DI float3 sky_radiance(const DevScene& S, const float3& dir, float ibl_intensity) {
+static HJ_NI float3 sky_radiance(const DevScene& S, const float3& dir, float ibl_intensity) {
     float4 c;
     if (S.ibl_w == 1 && S.ibl_h == 1) c = S.ibl[0];
     else {
