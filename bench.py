@@ -112,13 +112,21 @@ def cpu_arm(scene, cfg, budget_s=15.0, steps=1, warmup=0):
     o = ob.Oracle(scene, kind, xforms=xf, inv_xforms=inv)
     W, H = cfg["width"], cfg["height"]
     cores = os.cpu_count() or 1
-    spp_s = min(2, cfg["spp"])
-    # probe: 2 rows -> paths/s -> size the sample for ~budget_s
-    y0 = H // 2
+    spp_s = min(4, cfg["spp"])
+    # size the sample for ~budget_s of CPU work: grow the row band (then the spp) until one render takes >= budget/3
     fp = frame_for(scene, cfg, cfg["spp"], 0, spp_s)
-    t = time.time(); r = o.render(fp, threads=0, rows=(y0, y0 + 2)); dt = max(time.time() - t, 1e-3)
-    rows = int(max(2, min(H // 2, (budget_s / dt) * 2)))
-    rows -= rows % 2
+    rows = 8
+    while True:
+        y0 = (H - rows) // 2
+        t = time.time(); o.render(fp, threads=0, rows=(y0, y0 + rows)); dt = max(time.time() - t, 1e-3)
+        if dt >= budget_s / 3 or (rows >= H and spp_s >= cfg["spp"]):
+            break
+        grow = min(4.0, max(1.5, 0.8 * budget_s / dt))
+        if rows < H:
+            rows = int(min(H, rows * grow)); rows -= rows % 2
+        else:
+            spp_s = int(min(cfg["spp"], max(spp_s + 1, spp_s * grow)))
+            fp = frame_for(scene, cfg, cfg["spp"], 0, spp_s)
     y0 = (H - rows) // 2
     vals, last = [], None
     for i in range(warmup + steps):
@@ -153,7 +161,7 @@ def gpu_arm(args, rank, world, local_rank):
     r.build_accel(xf, inv)
     accel_ms = r.stats()["ms_accel"]
     # weak scaling: every rank renders `spp` samples; the frame has spp*world global sample indices
-    fp = frame_for(scene, cfg, spp * world, rank * spp, (rank + 1) * spp)
+    fp = frame_for(scene, cfg, *hj.weak_slice(spp, rank, world))
     if world > 1:
         import torch
         uid = [hj.Renderer.comm_unique_id() if rank == 0 else None]
@@ -201,8 +209,8 @@ def gpu_arm(args, rank, world, local_rank):
                data="synthetic", impl="ours",
                config=dict(workload=desc, triangles=scene.n_triangles, width=W, height=H, spp_per_gpu=spp, max_depth=cfg["max_depth"],
                            integrator="MIS", parallelism="sample slices, replicated scene, NCCL all-reduce of accum" if world > 1 else "single GPU",
-                           l2_policy="working set larger than L2: %.0f MB of path state + %.0f MB of BVH per pass, rewritten every bounce"
-                                     % (4 * (1 << 20) * 250 / 1e6, (r.stats()["bvh_nodes"] * 80 + scene.n_triangles * 48) / 1e6),
+                           l2_policy="inputs larger than L2 (126 MB): 8 pipelines x 2M paths x ~250 B of path state rewritten every bounce "
+                                     "+ %.0f MB of BVH nodes and triangles" % ((r.stats()["bvh_nodes"] * 80 + scene.n_triangles * 48) / 1e6),
                            timing="CUDA events on the context stream (N=1) / barrier-bracketed wall clock incl. all-reduce, max over ranks (N>1)"),
                spp_per_s=round(spp * world * args.steps / t_all, 3), rays_per_step=rays_all // args.steps,
                gpu_launches=launches_all, accel_build_ms=round(accel_ms, 3), clocks=clk, wall_s=round(wall, 3))
@@ -225,20 +233,31 @@ def gpu_arm(args, rank, world, local_rank):
         r.set_option("time_stages", 1); r.render(fp); stt = r.stats(); r.set_option("time_stages", 0)
         algo = 80.0 * sc["nodes_fetched"] + 48.0 * sc["tris_fetched"]
         nrays = sc["rays_extend"] + sc["rays_shadow"]
-        n_trace_launches = max(1, (st["kernel_launches"] - 1) // 1)
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        ach = algo / (stt["ms_trace"] / 1e3) / 1e9
+        # The timed region runs 8 wavefront pipelines concurrently, so a traversal launch has no private duration there.
+        # Its share of the GPU is taken from the event-pair pass, where every launch runs alone on one stream
+        # (share = sum of traversal launch durations / sum of all stage durations), and applied to the timed step.
+        share = stt["ms_trace"] / max(stt["ms_trace"] + stt["ms_shade"], 1e-9)
+        step_ms = 1e3 * t_all / args.steps
+        n_trace_launches = 3 * cfg["max_depth"] * max(1, -(-spp * W * H // (2 << 20)))
+        ach = algo / (share * step_ms / 1e3) / 1e9
+        ach_serial = algo / (stt["ms_trace"] / 1e3) / 1e9
         out["roofline"] = dict(bound="hbm", achieved=round(ach, 1), peak=peak, unit="GB/s", frac=round(ach / peak, 4), traffic=None,
                                peak_source="MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback",
-                               kernel="k_extend+k_shadow+k_mis (BVH traversal)", trace_ms_per_step=round(stt["ms_trace"], 3),
-                               shade_ms_per_step=round(stt["ms_shade"], 3), step_ms_timed_pass=round(stt["ms_render"], 3),
+                               kernel="k_trace<0|1|2> (BVH traversal: extend, shadow, MIS rays)",
+                               method="algorithmic bytes per step / (traversal share x timed step); share from the serial event-pair pass",
+                               trace_share=round(share, 4), achieved_serial_launches=round(ach_serial, 1),
+                               serial_trace_ms_per_step=round(stt["ms_trace"], 3), serial_shade_ms_per_step=round(stt["ms_shade"], 3),
+                               serial_step_ms=round(stt["ms_render"], 3), trace_launches_per_step=n_trace_launches,
+                               avg_launch_us_serial=round(1e3 * stt["ms_trace"] / n_trace_launches, 1),
                                nodes_per_ray=round(sc["nodes_fetched"] / nrays, 2), tris_per_ray=round(sc["tris_fetched"] / nrays, 2),
-                               bytes_per_ray=round(algo / nrays, 1), bound_mrays=round(peak * 1e9 / (algo / nrays) / 1e6, 1))
+                               bytes_per_ray=round(algo / nrays, 1), bound_mrays=round(peak * 1e9 / (algo / nrays) / 1e6, 1),
+                               max_nodes_one_ray=sc["max_nodes_per_ray"], max_tris_one_ray=sc["max_tris_per_ray"], bvh_depth=sc["bvh_depth"])
         if not args.no_cpu:
             vals, info = cpu_arm(scene, cfg, budget_s=args.cpu_budget)
             out["cpu_baseline"] = dict(value=round(vals[0], 3), unit="Mrays/s", cores=info["cores"], kind=info["kind"], sample=info["sample"],
