@@ -75,6 +75,63 @@ HJ_DI bool tri_test(const RayPrep& r, const float3& p0, const float3& p1, const 
 
 struct Hit { float t, b1, b2; uint32_t prim; };   // prim == 0xffffffff: miss
 
+// Intersects the 8 quantised child boxes of one 80-byte node with a ray: inner-child hits (bits 24..31, slot XOR octant
+// so that the highest bit is the nearest child) go to ng, triangle hits (bits 0..23, relative to tri_base) to tg.
+HJ_DI void node_boxes(const uint4* __restrict__ nodes, uint32_t node, const float3& o, const float3& idir, uint32_t oct,
+                      float tmin, float tcur, uint2& ng, uint2& tg) {
+    const uint4* N = nodes + 5 * (size_t)node;
+    const uint4 q0 = __ldg(N), q1 = __ldg(N + 1), q2 = __ldg(N + 2), q3 = __ldg(N + 3), q4 = __ldg(N + 4);
+    const float sx = __uint_as_float((q0.w & 0xffu) << 23), sy = __uint_as_float(((q0.w >> 8) & 0xffu) << 23),
+                sz = __uint_as_float(((q0.w >> 16) & 0xffu) << 23);
+    const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
+    const float ox = (__uint_as_float(q0.x) - o.x) * idir.x, oy = (__uint_as_float(q0.y) - o.y) * idir.y,
+                oz = (__uint_as_float(q0.z) - o.z) * idir.z;
+    // Plane distance t = q*a + o with q an 8-bit grid coordinate. q enters as the float 2^23+q (one PRMT, no
+    // int->float conversion) and the 2^23*a is folded into o: t = fma(2^23+q, a, o - 2^23 a). That costs half a grid
+    // cell of accuracy, so every slab is widened by one cell |a| plus a slack proportional to the magnitudes involved:
+    // rounding here can never cull a triangle that the (exact) triangle test accepts.
+    const float slack = 2e-6f * (fabsf(ox) + fabsf(oy) + fabsf(oz) + 255.0f * (fabsf(ax) + fabsf(ay) + fabsf(az)));
+    const float bx = 8388608.0f * ax, by = 8388608.0f * ay, bz = 8388608.0f * az;
+    const float oxn = (ox - slack - fabsf(ax)) - bx, oyn = (oy - slack - fabsf(ay)) - by, ozn = (oz - slack - fabsf(az)) - bz;
+    const float oxf = (ox + slack + fabsf(ax)) - bx, oyf = (oy + slack + fabsf(ay)) - by, ozf = (oz + slack + fabsf(az)) - bz;
+    const bool nx = (oct & 1u) != 0, ny = (oct & 2u) != 0, nz = (oct & 4u) != 0;
+    const uint32_t oct_inv4 = (oct ^ 7u) * 0x01010101u;
+    uint32_t k4b;                                   // 2^23 as bits, kept opaque so that PRMT's selector is the immediate
+    asm("mov.b32 %0, 0x4B000000;" : "=r"(k4b));
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const uint32_t lox = h ? q2.y : q2.x, loy = h ? q2.w : q2.z, loz = h ? q3.y : q3.x;
+        const uint32_t hix = h ? q3.w : q3.z, hiy = h ? q4.y : q4.x, hiz = h ? q4.w : q4.z;
+        const uint32_t meta4 = h ? q1.w : q1.z;
+        // four metas at once: inner children (bit index 24..31 = 0b11xxx) get their slot XORed with the octant
+        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = (is_inner4 >> 4) * 0x07u;
+        const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
+        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+        const uint32_t nearx = nx ? hix : lox, farx = nx ? lox : hix;
+        const uint32_t neary = ny ? hiy : loy, fary = ny ? loy : hiy;
+        const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint32_t sel = 0x7650u | (uint32_t)j;
+            const float tnx = __fmaf_rn(__uint_as_float(__byte_perm(nearx, k4b, sel)), ax, oxn);
+            const float tny = __fmaf_rn(__uint_as_float(__byte_perm(neary, k4b, sel)), ay, oyn);
+            const float tnz = __fmaf_rn(__uint_as_float(__byte_perm(nearz, k4b, sel)), az, ozn);
+            const float tfx = __fmaf_rn(__uint_as_float(__byte_perm(farx, k4b, sel)), ax, oxf);
+            const float tfy = __fmaf_rn(__uint_as_float(__byte_perm(fary, k4b, sel)), ay, oyf);
+            const float tfz = __fmaf_rn(__uint_as_float(__byte_perm(farz, k4b, sel)), az, ozf);
+            const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+            const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tcur));
+            const uint32_t bits = (child_bits4 >> (8 * j)) & 0xffu, idx = (bit_index4 >> (8 * j)) & 0xffu;
+            if (tn <= tf) hitmask |= bits << idx;      // empty slots have meta = 0
+        }
+    }
+    ng = make_uint2(q1.x, (hitmask & 0xff000000u) | (q0.w >> 24));
+    tg = make_uint2(q1.y, hitmask & 0x00ffffffu);
+}
+
+
 // Traversal state of one ray, advanced in two kinds of steps so that a warp can batch them: node_visit() intersects the
 // 8 quantised child boxes of the nearest pending inner child; tri_one() tests one pending triangle. Stack entries are
 // 8-byte groups (child_base, inner-hit bits 24..31 | imask).
@@ -111,58 +168,9 @@ struct Trav {
         const uint32_t slot = (k - 24u) ^ oct_inv;
         const uint32_t node = ng.x + __popc(ng.y & 0xffu & ((1u << slot) - 1u));
         if (ng.y > 0x00ffffffu) push(ng);
-        const uint4* N = S.nodes + 5 * (size_t)node;
-        const uint4 q0 = __ldg(N), q1 = __ldg(N + 1), q2 = __ldg(N + 2), q3 = __ldg(N + 3), q4 = __ldg(N + 4);
         if (COUNT) n_nodes++;
-        const float sx = __uint_as_float((q0.w & 0xffu) << 23), sy = __uint_as_float(((q0.w >> 8) & 0xffu) << 23),
-                    sz = __uint_as_float(((q0.w >> 16) & 0xffu) << 23);
-        const float ax = sx * r.idir.x, ay = sy * r.idir.y, az = sz * r.idir.z;
-        const float ox = (__uint_as_float(q0.x) - r.o.x) * r.idir.x, oy = (__uint_as_float(q0.y) - r.o.y) * r.idir.y,
-                    oz = (__uint_as_float(q0.z) - r.o.z) * r.idir.z;
-        // Plane distance t = q*a + o with q an 8-bit grid coordinate. q enters as the float 2^23+q (one PRMT, no
-        // int->float conversion) and the 2^23*a is folded into o: t = fma(2^23+q, a, o - 2^23 a). That costs half a grid
-        // cell of accuracy, so every slab is widened by one cell |a| plus a slack proportional to the magnitudes involved:
-        // rounding here can never cull a triangle that the (exact) triangle test accepts.
-        const float slack = 2e-6f * (fabsf(ox) + fabsf(oy) + fabsf(oz) + 255.0f * (fabsf(ax) + fabsf(ay) + fabsf(az)));
-        const float bx = 8388608.0f * ax, by = 8388608.0f * ay, bz = 8388608.0f * az;
-        const float oxn = (ox - slack - fabsf(ax)) - bx, oyn = (oy - slack - fabsf(ay)) - by, ozn = (oz - slack - fabsf(az)) - bz;
-        const float oxf = (ox + slack + fabsf(ax)) - bx, oyf = (oy + slack + fabsf(ay)) - by, ozf = (oz + slack + fabsf(az)) - bz;
         const float tcur = (best.prim != 0xffffffffu) ? best.t : tmax;
-        const bool nx = (r.oct & 1u) != 0, ny = (r.oct & 2u) != 0, nz = (r.oct & 4u) != 0;
-        const uint32_t oct_inv4 = oct_inv * 0x01010101u;
-        uint32_t k4b;                                   // 2^23 as bits, kept opaque so that PRMT's selector is the immediate
-        asm("mov.b32 %0, 0x4B000000;" : "=r"(k4b));
-        uint32_t hitmask = 0;
-#pragma unroll
-        for (int h = 0; h < 2; h++) {
-            const uint32_t lox = h ? q2.y : q2.x, loy = h ? q2.w : q2.z, loz = h ? q3.y : q3.x;
-            const uint32_t hix = h ? q3.w : q3.z, hiy = h ? q4.y : q4.x, hiz = h ? q4.w : q4.z;
-            const uint32_t meta4 = h ? q1.w : q1.z;
-            // four metas at once: inner children (bit index 24..31 = 0b11xxx) get their slot XORed with the octant
-            const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-            const uint32_t inner_mask4 = (is_inner4 >> 4) * 0x07u;
-            const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
-            const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-            const uint32_t nearx = nx ? hix : lox, farx = nx ? lox : hix;
-            const uint32_t neary = ny ? hiy : loy, fary = ny ? loy : hiy;
-            const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const uint32_t sel = 0x7650u | (uint32_t)j;
-                const float tnx = __fmaf_rn(__uint_as_float(__byte_perm(nearx, k4b, sel)), ax, oxn);
-                const float tny = __fmaf_rn(__uint_as_float(__byte_perm(neary, k4b, sel)), ay, oyn);
-                const float tnz = __fmaf_rn(__uint_as_float(__byte_perm(nearz, k4b, sel)), az, ozn);
-                const float tfx = __fmaf_rn(__uint_as_float(__byte_perm(farx, k4b, sel)), ax, oxf);
-                const float tfy = __fmaf_rn(__uint_as_float(__byte_perm(fary, k4b, sel)), ay, oyf);
-                const float tfz = __fmaf_rn(__uint_as_float(__byte_perm(farz, k4b, sel)), az, ozf);
-                const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
-                const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tcur));
-                const uint32_t bits = (child_bits4 >> (8 * j)) & 0xffu, idx = (bit_index4 >> (8 * j)) & 0xffu;
-                if (tn <= tf) hitmask |= bits << idx;      // empty slots have meta = 0
-            }
-        }
-        ng = make_uint2(q1.x, (hitmask & 0xff000000u) | (q0.w >> 24));
-        tg = make_uint2(q1.y, hitmask & 0x00ffffffu);
+        node_boxes(S.nodes, node, r.o, r.idir, r.oct, tmin, tcur, ng, tg);
     }
 
     // Tests one pending triangle (requires has_tris()). ANY: returns true on the first accepted hit.
@@ -194,4 +202,166 @@ HJ_DI Hit traverse(const DevScene& S, const float3& o, const float3& d, float tm
         while (t.has_tris()) if (t.tri_one<ANY, COUNT>(S, n_tris)) return t.best;
     }
     return t.best;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Warp-cooperative traversal (the loop every traversal kernel runs).
+//
+// Lanes own rays and walk the node hierarchy; the triangle tests they generate are NOT run by the owning lane: every
+// (owner lane, triangle) pair goes into a per-warp ring in shared memory and the warp tests 32 pairs at a time, one per
+// lane, whoever owns them. The owner's ray (origin + watertight shear) and its current best hit live in shared memory;
+// a tester merges a hit with one 64-bit atomicMin on the key (t bits << 32 | global primitive id) — exactly the
+// closest-hit rule (smaller t, ties -> lower id), so the result is still a pure function of (ray, scene). Lanes never
+// wait inside a triangle phase; r01-e measured 13-15 of 32 lanes per instruction with per-lane triangle tests.
+//   * a lane is finished when its node walk is done AND every pair it queued has been tested (ticket <= head);
+//   * rays are fetched dynamically: once REFILL_MIN lanes are idle the warp takes that many queue entries with one
+//     warp-aggregated atomicAdd.
+#ifndef HJ_QCAP
+#define HJ_QCAP 128          // ring entries per warp (power of two, >= 32 + 24)
+#endif
+#ifndef REFILL_MIN
+#define REFILL_MIN 8         // idle lanes before a warp fetches new rays
+#endif
+#ifndef TRACE_BURST
+#define TRACE_BURST 4        // node phases between refill checks
+#endif
+#ifndef WAIT_MAX
+#define WAIT_MAX 4           // lanes waiting for their last triangle tests that force a partial batch
+#endif
+#ifndef TRI_K
+#define TRI_K 2              // a batch runs once pending pairs >= min(32, TRI_K x lanes doing node work)
+#endif
+
+struct TraceShared {
+    uint2 stack[(HJ_SSTACK ? HJ_SSTACK : 1) * HJ_TRACE_THREADS];
+    uint32_t ray[9][HJ_TRACE_THREADS];              // ox oy oz Sx Sy Sz (kx | ky<<2 | kz<<4) tmin tmax
+    unsigned long long key[HJ_TRACE_THREADS];       // best hit: t bits << 32 | prim (miss: tmax bits << 32 | 0xffffffff)
+    float2 bary[HJ_TRACE_THREADS];                  // barycentrics of the best hit
+    uint32_t ring[HJ_TRACE_THREADS / 32][HJ_QCAP];  // pending pairs: owner lane | triangle (leaf order) << 5
+};
+
+// IO: uint32_t count; bool load(idx, o, d, tmin, tmax) (false: empty entry); void finish(const Hit&)
+template <bool ANY, bool COUNT, class IO>
+HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next, TraceShared& sh, uint2* l_stack,
+                           uint32_t& n_rays, uint32_t& n_nodes, uint32_t& n_tris, uint32_t* max_nodes, uint32_t* max_tris) {
+    const uint32_t FULL = 0xffffffffu;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, wbase = tid & ~31u;
+    uint32_t* ring = sh.ring[tid >> 5];
+    uint2* sstack = sh.stack + tid;
+    uint32_t head = 0, tail = 0;                    // warp-uniform absolute ring positions
+    uint32_t ticket = 0;                            // ring position after this lane's last queued pair
+    float3 o = f3(0.0f), idir = f3(0.0f); uint32_t oct = 0; float tmin = 0.0f;
+    uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u); int sp = 0;
+    bool active = false, exhausted = false;
+    uint32_t nn0 = 0, own_tris = 0;
+    while (true) {
+        const uint32_t idle = __ballot_sync(FULL, !active);
+        if (!exhausted && __popc(idle) >= REFILL_MIN) {
+            const int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(next, (uint32_t)__popc(idle));
+            base = __shfl_sync(FULL, base, leader);
+            if (!active) {
+                const uint32_t idx = base + __popc(idle & ((1u << lane) - 1u));
+                float3 d; float tmax;
+                if (idx < n && io.load(idx, o, d, tmin, tmax)) {
+                    const RayPrep r = prep_ray(o, d);
+                    idir = r.idir; oct = r.oct;
+                    sh.ray[0][tid] = __float_as_uint(o.x); sh.ray[1][tid] = __float_as_uint(o.y); sh.ray[2][tid] = __float_as_uint(o.z);
+                    sh.ray[3][tid] = __float_as_uint(r.Sx); sh.ray[4][tid] = __float_as_uint(r.Sy); sh.ray[5][tid] = __float_as_uint(r.Sz);
+                    sh.ray[6][tid] = (uint32_t)r.kx | ((uint32_t)r.ky << 2) | ((uint32_t)r.kz << 4);
+                    sh.ray[7][tid] = __float_as_uint(tmin); sh.ray[8][tid] = __float_as_uint(tmax);
+                    sh.key[tid] = ((unsigned long long)__float_as_uint(tmax) << 32) | 0xffffffffull;
+                    sh.bary[tid] = make_float2(0.0f, 0.0f);
+                    ng = make_uint2(0u, 0x80000000u);     // the root, as the only inner hit of a virtual parent
+                    tg = make_uint2(0u, 0u); sp = 0; ticket = head;
+                    active = true; nn0 = n_nodes; own_tris = 0;
+                }
+            }
+            if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
+        }
+        if (!__any_sync(FULL, active)) { if (exhausted) break; else continue; }
+#pragma unroll 1
+        for (int it = 0; it < TRACE_BURST; it++) {
+            // ---- node phase: every lane without un-queued triangles visits its nearest pending inner child
+            bool did = false;
+            if (active && tg.y == 0u) {
+                if (ng.y <= 0x00ffffffu && sp > 0) { sp--; ng = sp < HJ_SSTACK ? sstack[sp * HJ_TRACE_THREADS] : l_stack[sp - HJ_SSTACK]; }
+                if (ng.y > 0x00ffffffu) {
+                    const uint32_t k = 31u - (uint32_t)__clz(ng.y);      // highest bit = nearest (slots permuted by the octant)
+                    ng.y &= ~(1u << k);
+                    const uint32_t slot = (k - 24u) ^ (oct ^ 7u);
+                    const uint32_t node = ng.x + __popc(ng.y & 0xffu & ((1u << slot) - 1u));
+                    if (ng.y > 0x00ffffffu) { if (sp < HJ_SSTACK) sstack[sp * HJ_TRACE_THREADS] = ng; else l_stack[sp - HJ_SSTACK] = ng; sp++; }
+                    if (COUNT) n_nodes++;
+                    const float tcur = __uint_as_float((uint32_t)(sh.key[tid] >> 32));
+                    node_boxes(S.nodes, node, o, idir, oct, tmin, tcur, ng, tg);
+                    did = true;
+                }
+            }
+            // ---- queue the triangle hits: warp prefix sum of the counts, lanes that fit write (owner, triangle) pairs
+            const uint32_t cnt = active ? (uint32_t)__popc(tg.y) : 0u;
+            if (__any_sync(FULL, cnt != 0u)) {
+                uint32_t incl = cnt;
+#pragma unroll
+                for (int dlt = 1; dlt < 32; dlt <<= 1) { const uint32_t v = __shfl_up_sync(FULL, incl, dlt); if ((int)lane >= dlt) incl += v; }
+                const uint32_t room = HJ_QCAP - (tail - head);
+                const bool fit = incl <= room;                     // a prefix of the lanes
+                if (cnt != 0u && fit) {
+                    uint32_t m = tg.y, pos = tail + incl - cnt;
+                    while (m) {
+                        const uint32_t j = 31u - (uint32_t)__clz(m); m &= ~(1u << j);
+                        ring[pos++ & (HJ_QCAP - 1)] = lane | ((tg.x + j) << 5);
+                    }
+                    tg.y = 0u; ticket = pos; if (COUNT) own_tris += cnt;
+                }
+                tail += __reduce_max_sync(FULL, fit ? incl : 0u);
+                __syncwarp();
+            }
+            // ---- triangle phase: 32 pairs at a time, one per lane
+            const bool walked = active && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u;
+            const uint32_t waiting = __ballot_sync(FULL, walked && (int32_t)(head - ticket) < 0);
+            const uint32_t nwork = (uint32_t)__popc(__ballot_sync(FULL, did));
+            uint32_t thr = nwork * TRI_K; if (thr > 32u) thr = 32u; if (thr < 1u) thr = 1u;
+            if (__popc(waiting) >= WAIT_MAX) thr = 1u;
+            while (tail - head >= thr) {
+                uint32_t nb = tail - head; if (nb > 32u) nb = 32u;
+                bool hit = false; unsigned long long key = 0; uint32_t ow = 0; float b1 = 0.0f, b2 = 0.0f;
+                if (lane < nb) {
+                    const uint32_t e = ring[(head + lane) & (HJ_QCAP - 1)];
+                    ow = wbase + (e & 31u);
+                    if (!ANY || (uint32_t)sh.key[ow] == 0xffffffffu) {
+                        const float4* T = S.btris + 3 * (size_t)(e >> 5);
+                        const float4 v0 = __ldg(T), v1 = __ldg(T + 1), v2 = __ldg(T + 2);
+                        if (COUNT) n_tris++;
+                        RayPrep r;
+                        r.o = f3(__uint_as_float(sh.ray[0][ow]), __uint_as_float(sh.ray[1][ow]), __uint_as_float(sh.ray[2][ow]));
+                        r.Sx = __uint_as_float(sh.ray[3][ow]); r.Sy = __uint_as_float(sh.ray[4][ow]); r.Sz = __uint_as_float(sh.ray[5][ow]);
+                        const uint32_t kp = sh.ray[6][ow];
+                        r.kx = (int)(kp & 3u); r.ky = (int)((kp >> 2) & 3u); r.kz = (int)(kp >> 4);
+                        float t;
+                        if (tri_test(r, f3(v0), f3(v1), f3(v2), __uint_as_float(sh.ray[7][ow]), __uint_as_float(sh.ray[8][ow]), t, b1, b2)) {
+                            hit = true;
+                            key = ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)__float_as_uint(v0.w);
+                            atomicMin(&sh.key[ow], key);
+                        }
+                    }
+                }
+                __syncwarp();
+                if (hit && sh.key[ow] == key) sh.bary[ow] = make_float2(b1, b2);
+                __syncwarp();
+                head += nb;
+                thr = 32u;                                         // after a forced partial batch only full ones
+            }
+            // ---- any hit ends an occlusion ray; a finished lane hands its result over
+            if (ANY && active && (uint32_t)sh.key[tid] != 0xffffffffu) { ng.y = 0u; tg.y = 0u; sp = 0; }
+            if (active && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u && (int32_t)(head - ticket) >= 0) {
+                const unsigned long long k = sh.key[tid]; const float2 b = sh.bary[tid];
+                Hit h; h.t = __uint_as_float((uint32_t)(k >> 32)); h.prim = (uint32_t)k; h.b1 = b.x; h.b2 = b.y;
+                io.finish(h);
+                n_rays++; active = false;
+                if (COUNT) { atomicMax(max_nodes, n_nodes - nn0); atomicMax(max_tris, own_tris); }
+            }
+        }
+    }
 }

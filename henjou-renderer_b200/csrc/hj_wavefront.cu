@@ -287,6 +287,42 @@ HJ_DI void finish_mis(const DevScene& S, const FrameK& F, const WfPtrs& P, uint3
     P.L[slot] = f4(L, Lq.w + 1.0f);
 }
 
+#ifndef HJ_COOP
+#define HJ_COOP 1
+#endif
+#if HJ_COOP
+// MODE 0: extend (closest hit), 1: shadow (any hit), 2: MIS emitter ray (closest hit).
+// The warp loop (dynamic ray fetch, node phases, pooled 32-wide triangle tests) is trace_warp_loop in hj_trace.cuh.
+template <int MODE>
+struct WfRayIO {
+    const DevScene& S; const FrameK& F; const WfPtrs& P; const uint32_t* __restrict__ queue; uint32_t slot;
+    HJ_DI bool load(uint32_t idx, float3& o, float3& d, float& tmin, float& tmax) {
+        slot = queue[idx];
+        if (slot == 0xffffffffu) return false;
+        const float4 oq = MODE == 0 ? P.ray_o[slot] : (MODE == 1 ? P.sh_o[slot] : P.mi_o[slot]);
+        const float4 dq = MODE == 0 ? P.ray_d[slot] : (MODE == 1 ? P.sh_d[slot] : P.mi_d[slot]);
+        o = f3(oq); d = f3(dq); tmin = 0.001f; tmax = MODE == 1 ? oq.w : 1e16f;
+        return true;
+    }
+    HJ_DI void finish(const Hit& h) {
+        if (MODE == 0) finish_extend(F, P, slot, h);
+        else if (MODE == 1) finish_shadow(P, slot, h);
+        else finish_mis(S, F, P, slot, h);
+    }
+};
+
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace(DevScene S, FrameK F, WfPtrs P, int cur) {
+    __shared__ TraceShared sh;
+    uint2 l_stack[HJ_STACK];
+    const uint32_t n = MODE == 0 ? P.cnt->n_extend[cur] : (MODE == 1 ? P.cnt->n_shadow : P.cnt->n_mis);
+    WfRayIO<MODE> io{S, F, P, MODE == 0 ? P.q_ext[cur] : (MODE == 1 ? P.q_shadow : P.q_mis), 0u};
+    uint32_t nr = 0, nn = 0, nt = 0;
+    trace_warp_loop<MODE == 1, COUNT>(S, io, n, &P.cnt->next[MODE], sh, l_stack, nr, nn, nt, &P.cnt->max_nodes, &P.cnt->max_tris);
+    warp_add64(MODE == 1 ? &P.cnt->rays_shadow : &P.cnt->rays_extend, nr);
+    if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
+}
+#else
 // MODE 0: extend (closest hit), 1: shadow (any hit), 2: MIS emitter ray (closest hit)
 // The warp runs in lock step through two kinds of phases: a NODE phase (every lane without pending triangles visits
 // one node) and a TRIANGLE phase, entered only when at least TRI_BATCH lanes have pending triangles (or no lane can
@@ -357,6 +393,8 @@ __global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace(DevScene S,
     if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
 }
 
+#endif
+
 // ---------------------------------------------------------------------------------------------- accumulate / write-out
 __global__ void k_reset_queues(WfCounters* c, uint32_t n0, int all) {
     if (all) { c->n_extend[0] = n0; c->n_extend[1] = 0; }
@@ -397,34 +435,50 @@ __global__ void k_finalize(FrameK F, const float4* accum, float4* color, uchar4*
 }
 
 // ---------------------------------------------------------------------------------------------- batch trace (hj_trace)
+// runs the same warp loop as the integrator's traversal kernels (persistent grid, dynamic fetch, pooled triangle tests)
 template <bool ANY>
-__global__ void __launch_bounds__(WF_THREADS) k_trace_batch(DevScene S, const float4* rays, uint64_t n, uint32_t* prim, float* tuv) {
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float4 o = rays[2 * i], d = rays[2 * i + 1];
-    uint32_t nn = 0, nt = 0;
-    const Hit h = traverse<ANY, false>(S, f3(o), f3(d), o.w, d.w, nn, nt);
-    const bool hit = h.prim != 0xffffffffu;
-    if (ANY) prim[i] = hit ? 1u : 0xffffffffu;
-    else {
-        prim[i] = h.prim;
-        tuv[3 * i] = hit ? h.t : 0.0f; tuv[3 * i + 1] = hit ? h.b1 : 0.0f; tuv[3 * i + 2] = hit ? h.b2 : 0.0f;
+struct BatchRayIO {
+    const float4* __restrict__ rays; uint32_t* prim; float* tuv; uint32_t i;
+    HJ_DI bool load(uint32_t idx, float3& o, float3& d, float& tmin, float& tmax) {
+        i = idx;
+        const float4 oq = rays[2 * (size_t)idx], dq = rays[2 * (size_t)idx + 1];
+        o = f3(oq); d = f3(dq); tmin = oq.w; tmax = dq.w;
+        return true;
     }
+    HJ_DI void finish(const Hit& h) {
+        const bool hit = h.prim != 0xffffffffu;
+        if (ANY) prim[i] = hit ? 1u : 0xffffffffu;
+        else {
+            prim[i] = h.prim;
+            tuv[3 * (size_t)i] = hit ? h.t : 0.0f; tuv[3 * (size_t)i + 1] = hit ? h.b1 : 0.0f; tuv[3 * (size_t)i + 2] = hit ? h.b2 : 0.0f;
+        }
+    }
+};
+template <bool ANY>
+__global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace_batch(DevScene S, const float4* rays, uint32_t n, uint32_t* prim, float* tuv, uint32_t* cursor) {
+    __shared__ TraceShared sh;
+    uint2 l_stack[HJ_STACK];
+    BatchRayIO<ANY> io{rays, prim, tuv, 0u};
+    uint32_t nr = 0, nn = 0, nt = 0;
+    trace_warp_loop<ANY, false>(S, io, n, cursor, sh, l_stack, nr, nn, nt, nullptr, nullptr);
 }
 
 int hj_trace_batch(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, uint32_t* prim_host, float* tuv_host) {
     if (n == 0) return HJ_OK;
-    DevBuf dr, dp, dt;
-    HJ_CUDA(c, dr.reserve(n * 32)); HJ_CUDA(c, dp.reserve(n * 4)); HJ_CUDA(c, dt.reserve(n * 12));
+    if (n > 0x7fffffffull) { c->err = "hj_trace: at most 2^31-1 rays per call"; return HJ_ERR_INVALID; }
+    DevBuf dr, dp, dt, dc;
+    HJ_CUDA(c, dr.reserve(n * 32)); HJ_CUDA(c, dp.reserve(n * 4)); HJ_CUDA(c, dt.reserve(n * 12)); HJ_CUDA(c, dc.reserve(4));
     HJ_CUDA(c, cudaMemcpyAsync(dr.p, rays_host, n * 32, cudaMemcpyHostToDevice, c->stream));
-    const uint32_t grid = (uint32_t)((n + WF_THREADS - 1) / WF_THREADS);
-    if (any_hit) k_trace_batch<true><<<grid, WF_THREADS, 0, c->stream>>>(c->S, dr.as<float4>(), n, dp.as<uint32_t>(), dt.as<float>());
-    else k_trace_batch<false><<<grid, WF_THREADS, 0, c->stream>>>(c->S, dr.as<float4>(), n, dp.as<uint32_t>(), dt.as<float>());
+    HJ_CUDA(c, cudaMemsetAsync(dc.p, 0, 4, c->stream));
+    int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    const uint32_t grid = (uint32_t)std::min<uint64_t>((n + HJ_TRACE_THREADS - 1) / HJ_TRACE_THREADS, (uint64_t)sms * HJ_MINB);
+    if (any_hit) k_trace_batch<true><<<grid, HJ_TRACE_THREADS, 0, c->stream>>>(c->S, dr.as<float4>(), (uint32_t)n, dp.as<uint32_t>(), dt.as<float>(), dc.as<uint32_t>());
+    else k_trace_batch<false><<<grid, HJ_TRACE_THREADS, 0, c->stream>>>(c->S, dr.as<float4>(), (uint32_t)n, dp.as<uint32_t>(), dt.as<float>(), dc.as<uint32_t>());
     if (prim_host) HJ_CUDA(c, cudaMemcpyAsync(prim_host, dp.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
     if (tuv_host && !any_hit) HJ_CUDA(c, cudaMemcpyAsync(tuv_host, dt.p, n * 12, cudaMemcpyDeviceToHost, c->stream));
     HJ_CUDA(c, cudaStreamSynchronize(c->stream));
     HJ_CUDA(c, cudaGetLastError());
-    dr.release(); dp.release(); dt.release();
+    dr.release(); dp.release(); dt.release(); dc.release();
     return HJ_OK;
 }
 
