@@ -85,8 +85,18 @@ static HJ_NI float2 draw2(Sampler& s) {
     s.depth++;
     return r;
 }
-// cmj.h:130-133: burns a full 2-D draw
-HJ_DI float draw1(Sampler& s) { return draw2(s).x; }
+// cmj.h:130-133: cmj_1d burns a full 2-D draw and keeps x. Only the terms x depends on are evaluated (the sx permute
+// and the jy jitter feed y alone): same bits as draw2(s).x.
+static HJ_NI float draw1(Sampler& s) {
+    const uint32_t scr = xxhash32_u4(s.n_spp / 16u, s.image_idx, s.depth, s.scramble);
+    const uint32_t index = cmj_permute(s.n_spp % 16u, 16, scr * 0x51633e2d);
+    const uint32_t sy = cmj_permute(index / 4, 4, scr * 0x63d83595);
+    const float jx = cmj_randfloat(index, scr * 0xa399d265);
+    s.depth++;
+    return (index % 4 + (sy + jx) / 4) / 4;
+}
+// a draw whose value is never used (rt.h:266 / 426): only the dimension counter moves
+HJ_DI void draw_skip(Sampler& s) { s.depth++; }
 
 // ------------------------------------------------------------------ math.h
 // math.h:26-29

@@ -77,8 +77,13 @@ struct Hit { float t, b1, b2; uint32_t prim; };   // prim == 0xffffffff: miss
 
 // Intersects the 8 quantised child boxes of one 80-byte node with a ray: inner-child hits (bits 24..31, slot XOR octant
 // so that the highest bit is the nearest child) go to ng, triangle hits (bits 0..23, relative to tri_base) to tg.
+// k4b = bits of 2^23, which must sit in a REGISTER: PRMT takes one immediate, and that has to be the byte selector
+// (r01-g SASS: with a literal 2^23 ptxas kept the four selectors in registers instead, 45 extra moves per node).
+static __constant__ uint32_t c_two23 = 0x4B000000u;
+HJ_DI uint32_t load_two23() { return *(const volatile uint32_t*)&c_two23; }
+
 HJ_DI void node_boxes(const uint4* __restrict__ nodes, uint32_t node, const float3& o, const float3& idir, uint32_t oct,
-                      float tmin, float tcur, uint2& ng, uint2& tg) {
+                      float tmin, float tcur, uint32_t k4b, uint2& ng, uint2& tg) {
     const uint4* N = nodes + 5 * (size_t)node;
     const uint4 q0 = __ldg(N), q1 = __ldg(N + 1), q2 = __ldg(N + 2), q3 = __ldg(N + 3), q4 = __ldg(N + 4);
     const float sx = __uint_as_float((q0.w & 0xffu) << 23), sy = __uint_as_float(((q0.w >> 8) & 0xffu) << 23),
@@ -96,8 +101,6 @@ HJ_DI void node_boxes(const uint4* __restrict__ nodes, uint32_t node, const floa
     const float oxf = (ox + slack + fabsf(ax)) - bx, oyf = (oy + slack + fabsf(ay)) - by, ozf = (oz + slack + fabsf(az)) - bz;
     const bool nx = (oct & 1u) != 0, ny = (oct & 2u) != 0, nz = (oct & 4u) != 0;
     const uint32_t oct_inv4 = (oct ^ 7u) * 0x01010101u;
-    uint32_t k4b;                                   // 2^23 as bits, kept opaque so that PRMT's selector is the immediate
-    asm("mov.b32 %0, 0x4B000000;" : "=r"(k4b));
     uint32_t hitmask = 0;
 #pragma unroll
     for (int h = 0; h < 2; h++) {
@@ -170,7 +173,7 @@ struct Trav {
         if (ng.y > 0x00ffffffu) push(ng);
         if (COUNT) n_nodes++;
         const float tcur = (best.prim != 0xffffffffu) ? best.t : tmax;
-        node_boxes(S.nodes, node, r.o, r.idir, r.oct, tmin, tcur, ng, tg);
+        node_boxes(S.nodes, node, r.o, r.idir, r.oct, tmin, tcur, load_two23(), ng, tg);
     }
 
     // Tests one pending triangle (requires has_tris()). ANY: returns true on the first accepted hit.
@@ -254,7 +257,17 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
     uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u); int sp = 0;
     bool active = false, exhausted = false;
     uint32_t nn0 = 0, own_tris = 0;
+    const uint32_t k4b = load_two23();
     while (true) {
+        // ---- lanes whose walk is over and whose queued pairs are all tested hand their result over (once per burst,
+        //      so that the write-out runs several lanes wide)
+        if (active && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u && (int32_t)(head - ticket) >= 0) {
+            const unsigned long long k = sh.key[tid]; const float2 b = sh.bary[tid];
+            Hit h; h.t = __uint_as_float((uint32_t)(k >> 32)); h.prim = (uint32_t)k; h.b1 = b.x; h.b2 = b.y;
+            io.finish(h);
+            n_rays++; active = false;
+            if (COUNT) { atomicMax(max_nodes, n_nodes - nn0); atomicMax(max_tris, own_tris); }
+        }
         const uint32_t idle = __ballot_sync(FULL, !active);
         if (!exhausted && __popc(idle) >= REFILL_MIN) {
             const int leader = __ffs(idle) - 1;
@@ -295,7 +308,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                     if (ng.y > 0x00ffffffu) { if (sp < HJ_SSTACK) sstack[sp * HJ_TRACE_THREADS] = ng; else l_stack[sp - HJ_SSTACK] = ng; sp++; }
                     if (COUNT) n_nodes++;
                     const float tcur = __uint_as_float((uint32_t)(sh.key[tid] >> 32));
-                    node_boxes(S.nodes, node, o, idir, oct, tmin, tcur, ng, tg);
+                    node_boxes(S.nodes, node, o, idir, oct, tmin, tcur, k4b, ng, tg);
                     did = true;
                 }
             }
@@ -353,15 +366,8 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                 head += nb;
                 thr = 32u;                                         // after a forced partial batch only full ones
             }
-            // ---- any hit ends an occlusion ray; a finished lane hands its result over
+            // ---- any hit ends an occlusion ray
             if (ANY && active && (uint32_t)sh.key[tid] != 0xffffffffu) { ng.y = 0u; tg.y = 0u; sp = 0; }
-            if (active && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u && (int32_t)(head - ticket) >= 0) {
-                const unsigned long long k = sh.key[tid]; const float2 b = sh.bary[tid];
-                Hit h; h.t = __uint_as_float((uint32_t)(k >> 32)); h.prim = (uint32_t)k; h.b1 = b.x; h.b2 = b.y;
-                io.finish(h);
-                n_rays++; active = false;
-                if (COUNT) { atomicMax(max_nodes, n_nodes - nn0); atomicMax(max_tris, own_tris); }
-            }
         }
     }
 }

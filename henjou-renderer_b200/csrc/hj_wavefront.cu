@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(WF_THREADS) k_shade(DevScene S, FrameK F, WfPt
                             P.mi_a[slot] = f4(f, prd.is_specular ? 1.0f : 0.0f); P.mi_t[slot] = f4(thr, 0.0f);
                         }
                     }
-                    if (INTEG != HJ_INTEGRATOR_PT) (void)draw2(st);              // dead draw, rt.h:266 / 426
+                    if (INTEG != HJ_INTEGRATOR_PT) draw_skip(st);                // dead draw, rt.h:266 / 426
                     float pdf = 1.0f;
                     float3 lwi = f3(0.0f, 1.0f, 0.0f);
                     const float3 f = bsdf.sample(S, lwo, lwi, pdf, st);          // continuation, rt.h:141 / 269 / 429
