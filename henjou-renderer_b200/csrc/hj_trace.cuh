@@ -246,7 +246,8 @@ struct TraceShared {
 // IO: uint32_t count; bool load(idx, o, d, tmin, tmax) (false: empty entry); void finish(const Hit&)
 template <bool ANY, bool COUNT, class IO>
 HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next, TraceShared& sh, uint2* l_stack,
-                           uint32_t& n_rays, uint32_t& n_nodes, uint32_t& n_tris, uint32_t* max_nodes, uint32_t* max_tris) {
+                           uint32_t& n_rays, uint32_t& n_nodes, uint32_t& n_tris, uint32_t* max_nodes, uint32_t* max_tris,
+                           unsigned long long* diag = nullptr) {
     const uint32_t FULL = 0xffffffffu;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, wbase = tid & ~31u;
     uint32_t* ring = sh.ring[tid >> 5];
@@ -258,6 +259,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
     bool active = false, exhausted = false;
     uint32_t nn0 = 0, own_tris = 0;
     const uint32_t k4b = load_two23();
+    uint32_t d_ph = 0, d_act = 0, d_walk = 0, d_wait = 0, d_hold = 0, d_bat = 0, d_blanes = 0;
     while (true) {
         // ---- lanes whose walk is over and whose queued pairs are all tested hand their result over (once per burst,
         //      so that the write-out runs several lanes wide)
@@ -335,6 +337,10 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
             const bool walked = active && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u;
             const uint32_t waiting = __ballot_sync(FULL, walked && (int32_t)(head - ticket) < 0);
             const uint32_t nwork = (uint32_t)__popc(__ballot_sync(FULL, did));
+            if (COUNT && diag) {       // lane-state census per node phase: phases, active, walking, waiting, holding triangles
+                const uint32_t na = __popc(__ballot_sync(FULL, active)), nh = __popc(__ballot_sync(FULL, active && tg.y != 0u));
+                if (lane == 0) { d_ph++; d_act += na; d_walk += nwork; d_wait += __popc(waiting); d_hold += nh; }
+            }
             uint32_t thr = nwork * TRI_K; if (thr > 32u) thr = 32u; if (thr < 1u) thr = 1u;
             if (__popc(waiting) >= WAIT_MAX) thr = 1u;
             while (tail - head >= thr) {
@@ -364,10 +370,16 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                 if (hit && sh.key[ow] == key) sh.bary[ow] = make_float2(b1, b2);
                 __syncwarp();
                 head += nb;
+                if (COUNT && diag && lane == 0) { d_bat++; d_blanes += nb; }
                 thr = 32u;                                         // after a forced partial batch only full ones
             }
             // ---- any hit ends an occlusion ray
             if (ANY && active && (uint32_t)sh.key[tid] != 0xffffffffu) { ng.y = 0u; tg.y = 0u; sp = 0; }
         }
+    }
+    if (COUNT && diag && lane == 0) {
+        atomicAdd(diag + 0, (unsigned long long)d_ph); atomicAdd(diag + 1, (unsigned long long)d_act); atomicAdd(diag + 2, (unsigned long long)d_walk);
+        atomicAdd(diag + 3, (unsigned long long)d_wait); atomicAdd(diag + 4, (unsigned long long)d_hold);
+        atomicAdd(diag + 5, (unsigned long long)d_bat); atomicAdd(diag + 6, (unsigned long long)d_blanes);
     }
 }

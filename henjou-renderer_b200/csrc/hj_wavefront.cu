@@ -12,6 +12,7 @@
 // The draw order of every RNG dimension and the order of the float additions into the radiance follow the
 // reference loop exactly; rays whose contribution is exactly zero are not traced (they cannot change the result).
 #include "hj_ctx.h"
+#include <cstdlib>
 #include "hj_bsdf.cuh"
 #include "hj_trace.cuh"
 
@@ -20,6 +21,7 @@ struct WfCounters {
     uint32_t next[4];             // work-fetch cursors of the persistent traversal kernels (extend, shadow, mis)
     unsigned long long rays_extend, rays_shadow, nodes, tris;
     uint32_t max_nodes, max_tris;
+    unsigned long long diag[3][8];   // count_fetches: lane-state census of the traversal loop per ray type
 };
 
 struct FrameK {
@@ -318,7 +320,7 @@ __global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace(DevScene S,
     const uint32_t n = MODE == 0 ? P.cnt->n_extend[cur] : (MODE == 1 ? P.cnt->n_shadow : P.cnt->n_mis);
     WfRayIO<MODE> io{S, F, P, MODE == 0 ? P.q_ext[cur] : (MODE == 1 ? P.q_shadow : P.q_mis), 0u};
     uint32_t nr = 0, nn = 0, nt = 0;
-    trace_warp_loop<MODE == 1, COUNT>(S, io, n, &P.cnt->next[MODE], sh, l_stack, nr, nn, nt, &P.cnt->max_nodes, &P.cnt->max_tris);
+    trace_warp_loop<MODE == 1, COUNT>(S, io, n, &P.cnt->next[MODE], sh, l_stack, nr, nn, nt, &P.cnt->max_nodes, &P.cnt->max_tris, P.cnt->diag[MODE]);
     warp_add64(MODE == 1 ? &P.cnt->rays_shadow : &P.cnt->rays_extend, nr);
     if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
 }
@@ -526,7 +528,21 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     const bool timed = c->opt_time_stages != 0;
     // passes: whole samples of the whole frame; `np` pipelines keep that many passes in flight (1 when timing stages)
     int np = timed ? 1 : c->opt_pipelines;
-    uint64_t target = c->opt_paths_per_pass > 0 ? (uint64_t)c->opt_paths_per_pass : (2ull << 20);
+    // Pass size: the persistent traversal kernels keep ~150 k rays in flight and lose lanes while a queue drains, so a
+    // pass should be as large as memory allows (r01-i, C2 64 spp: 2 Mi paths 1320, 16 Mi paths 1465 Mrays/s). Auto: the
+    // frame split evenly over the pipelines, within half of the free device memory (~220 B of path state per slot).
+    uint64_t target = (uint64_t)c->opt_paths_per_pass;
+    if (c->opt_paths_per_pass <= 0) {
+        size_t mfree = 0, mtotal = 0;
+        cudaMemGetInfo(&mfree, &mtotal);
+        size_t held = 0;                                   // what the pipelines already own counts as available
+        for (int p = 0; p < HJ_MAX_PIPES; p++) for (int k = 0; c->wf[p].all[k]; k++) held += c->wf[p].all[k]->cap;
+        const uint64_t budget_slots = (uint64_t)((mfree + held) / 2) / 240ull / (uint64_t)np;
+        target = ((uint64_t)ns * WH + (uint64_t)np - 1) / (uint64_t)np;
+        if (target > budget_slots) target = budget_slots;
+        if (target > (64ull << 20)) target = 64ull << 20;
+        target += WH - 1;                                  // round up to whole samples
+    }
     uint32_t spass = (uint32_t)(target / WH); if (spass < 1) spass = 1; if (spass > ns && ns) spass = ns;
     if (spass * WH > 0xfffffff0ull) spass = (uint32_t)(0xfffffff0ull / WH);
     const uint32_t n_passes = ns ? (ns + spass - 1) / spass : 0;
@@ -653,7 +669,14 @@ int hj_wavefront_stats(hj_ctx* c) {
         HJ_CUDA(c, cudaMemcpy(&h, c->wf[p].counters.p, sizeof h, cudaMemcpyDeviceToHost));
         t.rays_extend += h.rays_extend; t.rays_shadow += h.rays_shadow; t.nodes += h.nodes; t.tris += h.tris;
         t.max_nodes = std::max(t.max_nodes, h.max_nodes); t.max_tris = std::max(t.max_tris, h.max_tris);
+        for (int m = 0; m < 3; m++) for (int k = 0; k < 8; k++) t.diag[m][k] += h.diag[m][k];
     }
+    if (c->opt_count_fetches && getenv("HJ_TRACE_DIAG"))
+        for (int m = 0; m < 3; m++) {
+            const unsigned long long* d = t.diag[m]; const double ph = d[0] ? (double)d[0] : 1.0;
+            fprintf(stderr, "[hj diag] ray type %d: node phases %llu, lanes/phase active %.2f walking %.2f waiting %.2f holding %.2f; "
+                    "triangle batches %llu, lanes/batch %.2f\n", m, d[0], d[1] / ph, d[2] / ph, d[3] / ph, d[4] / ph, d[5], d[5] ? (double)d[6] / d[5] : 0.0);
+        }
     c->stats.rays_extend = t.rays_extend; c->stats.rays_shadow = t.rays_shadow;
     c->stats.nodes_fetched = t.nodes; c->stats.tris_fetched = t.tris;
     c->stats.max_nodes_per_ray = t.max_nodes; c->stats.max_tris_per_ray = t.max_tris;
