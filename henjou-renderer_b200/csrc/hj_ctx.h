@@ -47,11 +47,13 @@ struct WavefrontState {
     cudaStream_t stream = nullptr; cudaEvent_t ev_acc = nullptr;
     DevBuf ray_o, ray_d, hit, thr, L, rng_depth, dbg;   // per-slot state (SoA)
     DevBuf q_extend[2], q_shadow, q_mis;                 // queues
+    DevBuf q_cls[3], q_ns, sf[4];                        // shade stages: per-class queues, non-specular queue, surface records
     DevBuf sh_o, sh_d, sh_c;      // shadow ray payload per slot: origin+tmax, dir, contribution
     DevBuf mi_o, mi_d, mi_a, mi_t;   // MIS ray payload per slot
     DevBuf counters;              // device-side queue counters + ray statistics
-    DevBuf* all[20] = {&ray_o, &ray_d, &hit, &thr, &L, &rng_depth, &dbg, &q_extend[0], &q_extend[1], &q_shadow, &q_mis,
-                       &sh_o, &sh_d, &sh_c, &mi_o, &mi_d, &mi_a, &mi_t, &counters, nullptr};
+    DevBuf* all[28] = {&ray_o, &ray_d, &hit, &thr, &L, &rng_depth, &dbg, &q_extend[0], &q_extend[1], &q_shadow, &q_mis,
+                       &sh_o, &sh_d, &sh_c, &mi_o, &mi_d, &mi_a, &mi_t, &counters, &q_cls[0], &q_cls[1], &q_cls[2], &q_ns,
+                       &sf[0], &sf[1], &sf[2], &sf[3], nullptr};
 };
 
 struct NcclApi;

@@ -135,78 +135,6 @@ HJ_DI void node_boxes(const uint4* __restrict__ nodes, uint32_t node, const floa
 }
 
 
-// Traversal state of one ray, advanced in two kinds of steps so that a warp can batch them: node_visit() intersects the
-// 8 quantised child boxes of the nearest pending inner child; tri_one() tests one pending triangle. Stack entries are
-// 8-byte groups (child_base, inner-hit bits 24..31 | imask).
-struct Trav {
-    RayPrep r; float tmin, tmax; Hit best;
-    uint2 ng, tg; int sp; uint32_t oct_inv;
-    uint2* sstack;                 // HJ_SSTACK entries in shared memory, strided by the block size (bank-conflict free)
-    uint2* stack;                  // overflow beyond HJ_SSTACK: HJ_STACK entries of local memory (declared by the kernel)
-    HJ_DI void push(const uint2 v) { if (sp < HJ_SSTACK) sstack[sp * HJ_TRACE_THREADS] = v; else stack[sp - HJ_SSTACK] = v; sp++; }
-    HJ_DI uint2 pop() { sp--; return sp < HJ_SSTACK ? sstack[sp * HJ_TRACE_THREADS] : stack[sp - HJ_SSTACK]; }
-
-    HJ_DI void init(const float3& o, const float3& d, float tmin_, float tmax_) {
-        r = prep_ray(o, d); tmin = tmin_; tmax = tmax_;
-        best.t = tmax_; best.b1 = best.b2 = 0.0f; best.prim = 0xffffffffu;
-        ng = make_uint2(0u, 0x80000000u);     // the root, as the only inner hit of a virtual parent
-        tg = make_uint2(0u, 0u); sp = 0; oct_inv = r.oct ^ 7u;
-    }
-    HJ_DI bool has_inner() const { return ng.y > 0x00ffffffu; }
-    HJ_DI bool has_tris() const { return tg.y != 0u; }
-    // makes an inner group current if there is one (pop); false: nothing left to visit
-    HJ_DI bool fetch_group() {
-        if (has_inner()) return true;
-        if (sp == 0) return false;
-        ng = pop();
-        return true;
-    }
-
-    // Visits the nearest remaining inner child of the current group (requires has_inner()): loads its 80-byte node and
-    // intersects the 8 child boxes; leaves the inner hits in ng and the triangle hits in tg.
-    template <bool COUNT>
-    HJ_DI void node_visit(const DevScene& S, uint32_t& n_nodes) {
-        const uint32_t k = 31u - (uint32_t)__clz(ng.y);          // highest bit = nearest (slots permuted by the ray octant)
-        ng.y &= ~(1u << k);
-        const uint32_t slot = (k - 24u) ^ oct_inv;
-        const uint32_t node = ng.x + __popc(ng.y & 0xffu & ((1u << slot) - 1u));
-        if (ng.y > 0x00ffffffu) push(ng);
-        if (COUNT) n_nodes++;
-        const float tcur = (best.prim != 0xffffffffu) ? best.t : tmax;
-        node_boxes(S.nodes, node, r.o, r.idir, r.oct, tmin, tcur, load_two23(), ng, tg);
-    }
-
-    // Tests one pending triangle (requires has_tris()). ANY: returns true on the first accepted hit.
-    template <bool ANY, bool COUNT>
-    HJ_DI bool tri_one(const DevScene& S, uint32_t& n_tris) {
-        const uint32_t j = 31u - (uint32_t)__clz(tg.y);
-        tg.y &= ~(1u << j);
-        const float4* T = S.btris + 3 * (size_t)(tg.x + j);
-        const float4 v0 = __ldg(T), v1 = __ldg(T + 1), v2 = __ldg(T + 2);
-        if (COUNT) n_tris++;
-        float t, b1, b2;
-        if (tri_test(r, f3(v0), f3(v1), f3(v2), tmin, tmax, t, b1, b2)) {
-            const uint32_t p = __float_as_uint(v0.w);
-            if (ANY) { best.t = t; best.b1 = b1; best.b2 = b2; best.prim = p; return true; }
-            if (best.prim == 0xffffffffu || t < best.t || (t == best.t && p < best.prim)) { best.t = t; best.b1 = b1; best.b2 = b2; best.prim = p; }
-        }
-        return false;
-    }
-};
-
-// whole-ray convenience wrapper (batch queries, tests): no warp batching
-template <bool ANY, bool COUNT>
-HJ_DI Hit traverse(const DevScene& S, const float3& o, const float3& d, float tmin, float tmax, uint32_t& n_nodes, uint32_t& n_tris) {
-    __shared__ uint2 s_stack[(HJ_SSTACK ? HJ_SSTACK : 1) * HJ_TRACE_THREADS];
-    uint2 l_stack[HJ_STACK];
-    Trav t; t.sstack = s_stack + threadIdx.x; t.stack = l_stack; t.init(o, d, tmin, tmax);
-    while (t.fetch_group()) {
-        t.node_visit<COUNT>(S, n_nodes);
-        while (t.has_tris()) if (t.tri_one<ANY, COUNT>(S, n_tris)) return t.best;
-    }
-    return t.best;
-}
-
 // ------------------------------------------------------------------------------------------------------------------
 // Warp-cooperative traversal (the loop every traversal kernel runs).
 //

@@ -18,6 +18,7 @@
 
 struct WfCounters {
     uint32_t n_extend[2]; uint32_t n_shadow, n_mis;
+    uint32_t n_cls[3], n_ns;      // shade-stage queues: Disney / EC-GGX / glass surfaces, and all non-specular ones
     uint32_t next[4];             // work-fetch cursors of the persistent traversal kernels (extend, shadow, mis)
     unsigned long long rays_extend, rays_shadow, nodes, tris;
     uint32_t max_nodes, max_tris;
@@ -32,7 +33,8 @@ struct FrameK {
 
 struct WfPtrs {
     float4 *ray_o, *ray_d, *hit, *thr, *L; uint32_t* rng; uint2* dbg;
-    uint32_t *q_ext[2], *q_shadow, *q_mis;
+    uint32_t *q_ext[2], *q_shadow, *q_mis, *q_cls[3], *q_ns;
+    float4 *sf0, *sf1, *sf2, *sf3;   // surface record per slot: (pos, roughness) (normal, metallic) (basecolor, sheen) (clearcoat, ior, flags, -)
     float4 *sh_o, *sh_d, *sh_c, *mi_o, *mi_d, *mi_a, *mi_t;
     WfCounters* cnt;
     float4 *aov_albedo, *aov_normal;
@@ -132,77 +134,158 @@ HJ_DI float light_pdf_area(const DevScene& S, uint32_t prim) {
     return 1.0f / (area * (int)S.n_lights);
 }
 
-// ---------------------------------------------------------------------------------------------- shade
-// One loop iteration of Pathtrace / NEE / MIS after the closest-hit query (rt.h:104-156 / 181-278 / 303-438),
-// followed by the Russian roulette that opens the NEXT iteration. INTEG: hj_integrator.
+// ---------------------------------------------------------------------------------------------- shade (staged)
+// One loop iteration of Pathtrace / NEE / MIS after the closest-hit query (rt.h:104-156 / 181-278 / 303-438), followed
+// by the Russian roulette that opens the NEXT iteration, as three small kernels instead of one 82 KB one: a monolithic
+// k_shade ran at 0.32 IPC with instruction-cache misses as its top stall and 15 of 32 lanes (r01-g) — straight-line code
+// executed once per path has no reuse in the 6 KB L0 / 32 KB L1.5 instruction caches. Stages:
+//   k_surface          closest-hit / miss programs: sky, emitter hits, AOVs, surface record, sort into class queues
+//   k_nee<INTEG>       light sample + BSDF evaluation -> shadow ray               (non-specular surfaces)
+//   k_sample<INTEG,C>  MIS BSDF sample -> MIS ray; dead draw; continuation sample; roulette   (one class C per launch)
+// Every stage derives its RNG dimension from the counter stored at the start of the iteration, so the draw order of
+// SURVEY §8 "draw ledger" is unchanged: [light pick, light barycentrics] [MIS sample] [dead] [continuation] [roulette].
+#ifndef HJ_SHADE_MINB
+#define HJ_SHADE_MINB 6
+#endif
+#define HJ_CLS_DISNEY 0
+#define HJ_CLS_GGX 1
+#define HJ_CLS_GLASS 2
+
+HJ_DI Surface load_surface(const WfPtrs& P, uint32_t slot) {
+    const float4 r0 = P.sf0[slot], r1 = P.sf1[slot], r2 = P.sf2[slot], r3 = P.sf3[slot];
+    Surface s;
+    s.position = f3(r0); s.roughness = r0.w; s.normal = f3(r1); s.metallic = r1.w; s.basecolor = f3(r2); s.sheen = r2.w;
+    s.clearcoat = r3.x; s.ior = r3.y;
+    const uint32_t fl = __float_as_uint(r3.z);
+    s.is_specular = (fl & 1u) != 0; s.is_thinfilm = (fl & 2u) != 0; s.is_light = false; s.emission = f3(0.0f);
+    return s;
+}
+
 template <int INTEG>
-__global__ void __launch_bounds__(WF_THREADS) k_shade(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
+__global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_surface(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
     const uint32_t n = P.cnt->n_extend[cur];
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
         const uint32_t slot = (i < n) ? P.q_ext[cur][i] : 0xffffffffu;
-        bool push_shadow = false, push_mis = false, push_next = false;
+        int cls = -1;
         if (slot != 0xffffffffu) {
             const float4 hq = P.hit[slot];
             const uint32_t prim = __float_as_uint(hq.w);
-            const float3 d = f3(P.ray_d[slot]);
-            float3 thr = f3(P.thr[slot]);
-            const float4 Lq = P.L[slot];
-            float3 L = f3(Lq);
             const uint32_t pix = slot % F.WH;
-            Sampler st; st.n_spp = s0 + slot / F.WH; st.scramble = F.frame; st.image_idx = pix; st.depth = P.rng[slot];
-            const bool first_sample = (depth == 0 && st.n_spp == 0);
+            const bool first_sample = (depth == 0 && s0 + slot / F.WH == 0);
             if (prim == 0xffffffffu) {                               // __miss__ms (D6); AOVs stay 0 (raygen wrote them)
-                const float3 em = sky_radiance(S, d, F.ibl);
-                if (INTEG == HJ_INTEGRATOR_PT || depth == 0) { L += thr * em; P.L[slot] = f4(L, Lq.w); }
+                if (INTEG == HJ_INTEGRATOR_PT || depth == 0) {
+                    const float3 em = sky_radiance(S, f3(P.ray_d[slot]), F.ibl);
+                    const float4 Lq = P.L[slot];
+                    P.L[slot] = f4(f3(Lq) + f3(P.thr[slot]) * em, Lq.w);
+                }
             } else {
                 const Surface prd = make_surface(S, prim, hq.y, hq.z);
                 if (first_sample) { P.aov_albedo[pix] = f4(prd.basecolor, 1.0f); P.aov_normal[pix] = f4(prd.normal, 1.0f); }   // rt.h:113-116
                 if (prd.is_light) {
-                    if (INTEG == HJ_INTEGRATOR_PT || depth == 0) { L += thr * prd.emission; P.L[slot] = f4(L, Lq.w); }
+                    if (INTEG == HJ_INTEGRATOR_PT || depth == 0) {
+                        const float4 Lq = P.L[slot];
+                        P.L[slot] = f4(f3(Lq) + f3(P.thr[slot]) * prd.emission, Lq.w);
+                    }
                 } else {
-                    SurfaceBsdf bsdf; bsdf.init(prd);
-                    float3 t, b; const float3 nrm = prd.normal;
-                    onb(nrm, t, b);
-                    const float3 lwo = to_local(-d, t, nrm, b);
-                    if (INTEG != HJ_INTEGRATOR_PT && S.n_lights >= 1) {          // light sampling, rt.h:219-260 / 341-380
-                        float lpdf; float3 lnrm, lem;
-                        const float3 lpos = sample_light(S, st, lpdf, lnrm, lem);
-                        float3 ld = lpos - prd.position;
-                        const float dist = length(ld);
-                        ld = normalize(ld);
-                        const float c1 = absdot(nrm, ld), c2 = absdot(lnrm, -ld);
-                        const float3 lwi = to_local(ld, t, nrm, b);
-                        const float3 f = bsdf.eval(S, lwo, lwi);
-                        const float G = c2 / (dist * dist);
-                        float3 contrib;
-                        if (INTEG == HJ_INTEGRATOR_MIS) {
-                            const float ppdf = bsdf.pdf(lwo, lwi) * G;
-                            const float w = lpdf / (lpdf + ppdf);
-                            contrib = thr * (f * G * c1 / lpdf) * w * lem;
-                        } else contrib = thr * (f * G * c1 / lpdf) * lem;
-                        if (!is_zero3(contrib)) {
-                            push_shadow = true;
-                            P.sh_o[slot] = f4(prd.position, dist - 0.001f); P.sh_d[slot] = f4(ld, 0.0f); P.sh_c[slot] = f4(contrib, 0.0f);
-                        }
+                    P.sf0[slot] = f4(prd.position, prd.roughness); P.sf1[slot] = f4(prd.normal, prd.metallic);
+                    P.sf2[slot] = f4(prd.basecolor, prd.sheen);
+                    P.sf3[slot] = make_float4(prd.clearcoat, prd.ior, __uint_as_float((prd.is_specular ? 1u : 0u) | (prd.is_thinfilm ? 2u : 0u)), 0.0f);
+                    cls = prd.is_specular ? HJ_CLS_GLASS : (prd.metallic > 0.5 ? HJ_CLS_GGX : HJ_CLS_DISNEY);   // BSDFs.h:995-1030
+                }
+            }
+        }
+        queue_push(&P.cnt->n_cls[HJ_CLS_DISNEY], P.q_cls[HJ_CLS_DISNEY], cls == HJ_CLS_DISNEY, slot);
+        queue_push(&P.cnt->n_cls[HJ_CLS_GGX], P.q_cls[HJ_CLS_GGX], cls == HJ_CLS_GGX, slot);
+        queue_push(&P.cnt->n_cls[HJ_CLS_GLASS], P.q_cls[HJ_CLS_GLASS], cls == HJ_CLS_GLASS, slot);
+        if (INTEG != HJ_INTEGRATOR_PT) queue_push(&P.cnt->n_ns, P.q_ns, cls == HJ_CLS_DISNEY || cls == HJ_CLS_GGX, slot);
+    }
+}
+
+// light sampling + BSDF evaluation of the non-specular surfaces (rt.h:219-260 / 341-380). Specular surfaces evaluate to
+// zero (BSDFs.h:1006-1013), so their light sample contributes nothing and only moves the RNG counter (k_sample skips it).
+template <int INTEG>
+__global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_nee(DevScene S, FrameK F, WfPtrs P, uint32_t s0) {
+    const uint32_t n = P.cnt->n_ns;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
+        const uint32_t slot = (i < n) ? P.q_ns[i] : 0xffffffffu;
+        bool push_shadow = false;
+        if (slot != 0xffffffffu) {
+            const Surface prd = load_surface(P, slot);
+            const float3 d = f3(P.ray_d[slot]), thr = f3(P.thr[slot]);
+            Sampler st; st.n_spp = s0 + slot / F.WH; st.scramble = F.frame; st.image_idx = slot % F.WH; st.depth = P.rng[slot];
+            Disney bsdf; bsdf.init(prd);
+            float3 t, b; const float3 nrm = prd.normal;
+            onb(nrm, t, b);
+            const float3 lwo = to_local(-d, t, nrm, b);
+            float lpdf; float3 lnrm, lem;
+            const float3 lpos = sample_light(S, st, lpdf, lnrm, lem);
+            float3 ld = lpos - prd.position;
+            const float dist = length(ld);
+            ld = normalize(ld);
+            const float c1 = absdot(nrm, ld), c2 = absdot(lnrm, -ld);
+            const float3 lwi = to_local(ld, t, nrm, b);
+            const float3 f = bsdf.eval(S, lwo, lwi);
+            const float G = c2 / (dist * dist);
+            float3 contrib;
+            if (INTEG == HJ_INTEGRATOR_MIS) {
+                const float ppdf = bsdf.pdf(lwo, lwi) * G;
+                const float w = lpdf / (lpdf + ppdf);
+                contrib = thr * (f * G * c1 / lpdf) * w * lem;
+            } else contrib = thr * (f * G * c1 / lpdf) * lem;
+            if (!is_zero3(contrib)) {
+                push_shadow = true;
+                P.sh_o[slot] = f4(prd.position, dist - 0.001f); P.sh_d[slot] = f4(ld, 0.0f); P.sh_c[slot] = f4(contrib, 0.0f);
+            }
+        }
+        queue_push(&P.cnt->n_shadow, P.q_shadow, push_shadow, slot);
+    }
+}
+
+// BSDF sampling of one surface class: [MIS only] a sample towards emitters (rt.h:383-420) -> MIS ray; the dead draw
+// (rt.h:266 / 426); the continuation sample (rt.h:141 / 269 / 429), throughput update and the roulette of the next
+// iteration. The two samples run through the same code (a 2-trip loop, not unrolled).
+template <int CLS>
+HJ_DI float3 sample_class(const DevScene& S, const Surface& prd, const float3& lwo, float3& lwi, float& pdf, Sampler& st) {
+    if (CLS == HJ_CLS_GLASS) return metaglass_sample(f3(1.0f), prd.ior, lwo, lwi, pdf, st);
+    if (CLS == HJ_CLS_GGX) { MultiScatterGGX g; g.init(prd.basecolor, prd.roughness); return g.sample(lwo, lwi, st, pdf); }
+    Disney dz; dz.init(prd);
+    return dz.sample(S, lwo, lwi, pdf, st);
+}
+
+template <int INTEG, int CLS>
+__global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
+    const uint32_t n = P.cnt->n_cls[CLS];
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
+        const uint32_t slot = (i < n) ? P.q_cls[CLS][i] : 0xffffffffu;
+        bool push_mis = false, push_next = false;
+        if (slot != 0xffffffffu) {
+            const Surface prd = load_surface(P, slot);
+            const float3 d = f3(P.ray_d[slot]);
+            float3 thr = f3(P.thr[slot]);
+            Sampler st; st.n_spp = s0 + slot / F.WH; st.scramble = F.frame; st.image_idx = slot % F.WH; st.depth = P.rng[slot];
+            if (INTEG != HJ_INTEGRATOR_PT && S.n_lights >= 1) st.depth += 2;     // light pick + barycentrics (light_sample.h:18,60)
+            float3 t, b; const float3 nrm = prd.normal;
+            onb(nrm, t, b);
+            const float3 lwo = to_local(-d, t, nrm, b);
+            if (INTEG == HJ_INTEGRATOR_NEE) draw_skip(st);                      // dead draw, rt.h:266
+#pragma unroll 1
+            for (int k = (INTEG == HJ_INTEGRATOR_MIS ? 0 : 1); k < 2; k++) {
+                float pdf = 1.0f;                   // defined (reference: uninitialised in MIS)
+                float3 lwi = f3(0.0f, 1.0f, 0.0f);  // defined (reference: uninitialised in MIS)
+                const float3 f = sample_class<CLS>(S, prd, lwo, lwi, pdf, st);
+                const float3 wi = to_world(lwi, t, nrm, b);
+                if (k == 0) {
+                    const float c1 = absdot(wi, nrm);
+                    if (!is_zero3(f * c1)) {
+                        push_mis = true;
+                        P.mi_o[slot] = f4(prd.position, c1); P.mi_d[slot] = f4(wi, pdf);
+                        P.mi_a[slot] = f4(f, prd.is_specular ? 1.0f : 0.0f); P.mi_t[slot] = f4(thr, 0.0f);
                     }
-                    if (INTEG == HJ_INTEGRATOR_MIS) {                            // BSDF sampling towards emitters, rt.h:383-420
-                        float ppdf = 1.0f;                  // defined (reference: uninitialised)
-                        float3 lwi = f3(0.0f, 1.0f, 0.0f);  // defined (reference: uninitialised)
-                        const float3 f = bsdf.sample(S, lwo, lwi, ppdf, st);
-                        const float3 wi = to_world(lwi, t, nrm, b);
-                        const float c1 = absdot(wi, nrm);
-                        if (!is_zero3(f * c1)) {
-                            push_mis = true;
-                            P.mi_o[slot] = f4(prd.position, c1); P.mi_d[slot] = f4(wi, ppdf);
-                            P.mi_a[slot] = f4(f, prd.is_specular ? 1.0f : 0.0f); P.mi_t[slot] = f4(thr, 0.0f);
-                        }
-                    }
-                    if (INTEG != HJ_INTEGRATOR_PT) draw_skip(st);                // dead draw, rt.h:266 / 426
-                    float pdf = 1.0f;
-                    float3 lwi = f3(0.0f, 1.0f, 0.0f);
-                    const float3 f = bsdf.sample(S, lwo, lwi, pdf, st);          // continuation, rt.h:141 / 269 / 429
-                    const float3 wi = to_world(lwi, t, nrm, b);
+                    draw_skip(st);                                               // dead draw, rt.h:426
+                } else {
                     thr *= f * fabsf(dot(wi, nrm)) / pdf;
                     if (depth + 1 < F.max_depth && roulette(thr, st)) {          // opens iteration depth+1
                         push_next = true;
@@ -212,32 +295,18 @@ __global__ void __launch_bounds__(WF_THREADS) k_shade(DevScene S, FrameK F, WfPt
                 }
             }
         }
-        queue_push(&P.cnt->n_shadow, P.q_shadow, push_shadow, slot);
-        queue_push(&P.cnt->n_mis, P.q_mis, push_mis, slot);
+        if (INTEG == HJ_INTEGRATOR_MIS) queue_push(&P.cnt->n_mis, P.q_mis, push_mis, slot);
         queue_push(&P.cnt->n_extend[cur ^ 1], P.q_ext[cur ^ 1], push_next, slot);
     }
 }
-
 // ---------------------------------------------------------------------------------------------- traversal kernels
 // One persistent kernel per ray type (the reference's two optixTrace call sites, rt.h:53 RayTrace and rt.h:25
 // TraceOcculution, plus the MIS emitter ray rt.h:389). Warps fetch rays from the queue dynamically: a lane whose ray
 // has finished idles only until the warp has lost LOST_MAX lane-iterations, then the warp refills every idle lane
 // with one warp-aggregated atomic — this keeps the SIMD lanes busy although ray lengths differ by 10x.
 #ifndef HJ_MINB
-#define HJ_MINB 8
+#define HJ_MINB 8      // resident blocks per SM of the traversal kernels (64 registers)
 #endif
-#ifndef REFILL_MIN
-#define REFILL_MIN 8
-#endif
-#ifndef TRACE_BURST
-#define TRACE_BURST 4
-#endif
-#ifndef TRI_BATCH
-#define TRI_BATCH 8
-#endif
-//#define REFILL_MIN 8     // idle lanes before a warp fetches new rays
-// REFILL_MIN: idle lanes before a warp fetches new rays; TRACE_BURST: phases between refill checks;
-// TRI_BATCH: lanes with pending triangles that trigger a triangle phase
 
 HJ_DI void finish_extend(const FrameK& F, const WfPtrs& P, uint32_t slot, const Hit& h) {
     P.hit[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.prim));
@@ -289,10 +358,6 @@ HJ_DI void finish_mis(const DevScene& S, const FrameK& F, const WfPtrs& P, uint3
     P.L[slot] = f4(L, Lq.w + 1.0f);
 }
 
-#ifndef HJ_COOP
-#define HJ_COOP 1
-#endif
-#if HJ_COOP
 // MODE 0: extend (closest hit), 1: shadow (any hit), 2: MIS emitter ray (closest hit).
 // The warp loop (dynamic ray fetch, node phases, pooled 32-wide triangle tests) is trace_warp_loop in hj_trace.cuh.
 template <int MODE>
@@ -324,85 +389,17 @@ __global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace(DevScene S,
     warp_add64(MODE == 1 ? &P.cnt->rays_shadow : &P.cnt->rays_extend, nr);
     if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
 }
-#else
-// MODE 0: extend (closest hit), 1: shadow (any hit), 2: MIS emitter ray (closest hit)
-// The warp runs in lock step through two kinds of phases: a NODE phase (every lane without pending triangles visits
-// one node) and a TRIANGLE phase, entered only when at least TRI_BATCH lanes have pending triangles (or no lane can
-// do node work): triangle tests are long and rare per node, so batching them across lanes is what keeps them from
-// running 3 lanes wide.
-template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace(DevScene S, FrameK F, WfPtrs P, int cur) {
-    __shared__ uint2 s_stack[(HJ_SSTACK ? HJ_SSTACK : 1) * HJ_TRACE_THREADS];
-    const uint32_t n = MODE == 0 ? P.cnt->n_extend[cur] : (MODE == 1 ? P.cnt->n_shadow : P.cnt->n_mis);
-    const uint32_t* __restrict__ queue = MODE == 0 ? P.q_ext[cur] : (MODE == 1 ? P.q_shadow : P.q_mis);
-    uint32_t* next = &P.cnt->next[MODE];
-    const uint32_t lane = threadIdx.x & 31u;
-    constexpr bool ANY = MODE == 1;
-    uint2 l_stack[HJ_STACK];
-    Trav t; t.sstack = s_stack + threadIdx.x; t.stack = l_stack;
-    bool active = false, exhausted = false;
-    uint32_t slot = 0, nn = 0, nt = 0, nr = 0, nn0 = 0, nt0 = 0;
-    while (true) {
-        const uint32_t idle = __ballot_sync(0xffffffffu, !active);
-        if (!exhausted && __popc(idle) >= REFILL_MIN) {
-            const int leader = __ffs(idle) - 1;
-            uint32_t base = 0;
-            if ((int)lane == leader) base = atomicAdd(next, (uint32_t)__popc(idle));
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (!active) {
-                const uint32_t idx = base + __popc(idle & ((1u << lane) - 1u));
-                if (idx < n) {
-                    slot = queue[idx];
-                    if (slot != 0xffffffffu) {
-                        if (MODE == 0) { const float4 o = P.ray_o[slot], d = P.ray_d[slot]; t.init(f3(o), f3(d), 0.001f, 1e16f); }
-                        else if (MODE == 1) { const float4 o = P.sh_o[slot], d = P.sh_d[slot]; t.init(f3(o), f3(d), 0.001f, o.w); }
-                        else { const float4 o = P.mi_o[slot], d = P.mi_d[slot]; t.init(f3(o), f3(d), 0.001f, 1e16f); }
-                        active = true; nn0 = nn; nt0 = nt;
-                    }
-                }
-            }
-            if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
-        }
-        if (!__any_sync(0xffffffffu, active)) { if (exhausted) break; else continue; }
-#pragma unroll 1
-        for (int it = 0; it < TRACE_BURST; it++) {
-            // ---- node phase
-            bool done = false;
-            if (active && !t.has_tris()) {
-                if (t.fetch_group()) t.node_visit<COUNT>(S, nn);
-                else done = true;
-            }
-            // ---- triangle phase, batched
-            uint32_t tl = __ballot_sync(0xffffffffu, active && t.has_tris());
-            const uint32_t nl = __ballot_sync(0xffffffffu, active && !done && !t.has_tris());
-            if (tl && (__popc(tl) >= TRI_BATCH || nl == 0u)) {
-                const int keep = nl == 0u ? 1 : TRI_BATCH / 2;
-                do {
-                    if (active && t.has_tris()) { if (t.tri_one<ANY, COUNT>(S, nt)) { t.tg.y = 0u; t.ng.y = 0u; t.sp = 0; } }
-                    tl = __ballot_sync(0xffffffffu, active && t.has_tris());
-                } while (__popc(tl) >= keep);
-            }
-            if (done) {
-                if (MODE == 0) finish_extend(F, P, slot, t.best);
-                else if (MODE == 1) finish_shadow(P, slot, t.best);
-                else finish_mis(S, F, P, slot, t.best);
-                nr++; active = false;
-                if (COUNT) { atomicMax(&P.cnt->max_nodes, nn - nn0); atomicMax(&P.cnt->max_tris, nt - nt0); }
-            }
-        }
-    }
-    warp_add64(MODE == 1 ? &P.cnt->rays_shadow : &P.cnt->rays_extend, nr);
-    if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
-}
-
-#endif
 
 // ---------------------------------------------------------------------------------------------- accumulate / write-out
 __global__ void k_reset_queues(WfCounters* c, uint32_t n0, int all) {
     if (all) { c->n_extend[0] = n0; c->n_extend[1] = 0; }
     c->n_shadow = 0; c->n_mis = 0; c->next[0] = c->next[1] = c->next[2] = 0;
+    c->n_cls[0] = c->n_cls[1] = c->n_cls[2] = c->n_ns = 0;
 }
-__global__ void k_swap_queues(WfCounters* c, int cur) { c->n_extend[cur] = 0; c->n_shadow = 0; c->n_mis = 0; c->next[0] = c->next[1] = c->next[2] = 0; }
+__global__ void k_swap_queues(WfCounters* c, int cur) {
+    c->n_extend[cur] = 0; c->n_shadow = 0; c->n_mis = 0; c->next[0] = c->next[1] = c->next[2] = 0;
+    c->n_cls[0] = c->n_cls[1] = c->n_cls[2] = c->n_ns = 0;
+}
 
 // end of a pass: per pixel, add the pass's samples in sample order (same float addition order as the
 // reference's spp loop), and export the per-path debug records
@@ -494,6 +491,9 @@ static int wf_reserve(hj_ctx* c, WavefrontState& w, uint32_t cap, bool mis, bool
     HJ_CUDA(c, w.dbg.reserve(debug ? (size_t)cap * 8 : 8));
     HJ_CUDA(c, w.q_extend[0].reserve((size_t)cap * 4)); HJ_CUDA(c, w.q_extend[1].reserve((size_t)cap * 4));
     HJ_CUDA(c, w.q_shadow.reserve((size_t)cap * 4)); HJ_CUDA(c, w.q_mis.reserve((size_t)cap * 4));
+    for (int k = 0; k < 3; k++) HJ_CUDA(c, w.q_cls[k].reserve((size_t)cap * 4));
+    HJ_CUDA(c, w.q_ns.reserve((size_t)cap * 4));
+    for (int k = 0; k < 4; k++) HJ_CUDA(c, w.sf[k].reserve(f4s));
     HJ_CUDA(c, w.sh_o.reserve(f4s)); HJ_CUDA(c, w.sh_d.reserve(f4s)); HJ_CUDA(c, w.sh_c.reserve(f4s));
     if (mis) { HJ_CUDA(c, w.mi_o.reserve(f4s)); HJ_CUDA(c, w.mi_d.reserve(f4s)); HJ_CUDA(c, w.mi_a.reserve(f4s)); HJ_CUDA(c, w.mi_t.reserve(f4s)); }
     HJ_CUDA(c, w.counters.reserve(sizeof(WfCounters)));
@@ -509,11 +509,31 @@ static WfPtrs wf_ptrs(hj_ctx* c, WavefrontState& w) {
     P.L = w.L.as<float4>(); P.rng = w.rng_depth.as<uint32_t>(); P.dbg = w.dbg.as<uint2>();
     P.q_ext[0] = w.q_extend[0].as<uint32_t>(); P.q_ext[1] = w.q_extend[1].as<uint32_t>();
     P.q_shadow = w.q_shadow.as<uint32_t>(); P.q_mis = w.q_mis.as<uint32_t>();
+    for (int k = 0; k < 3; k++) P.q_cls[k] = w.q_cls[k].as<uint32_t>();
+    P.q_ns = w.q_ns.as<uint32_t>();
+    P.sf0 = w.sf[0].as<float4>(); P.sf1 = w.sf[1].as<float4>(); P.sf2 = w.sf[2].as<float4>(); P.sf3 = w.sf[3].as<float4>();
     P.sh_o = w.sh_o.as<float4>(); P.sh_d = w.sh_d.as<float4>(); P.sh_c = w.sh_c.as<float4>();
     P.mi_o = w.mi_o.as<float4>(); P.mi_d = w.mi_d.as<float4>(); P.mi_a = w.mi_a.as<float4>(); P.mi_t = w.mi_t.as<float4>();
     P.cnt = w.counters.as<WfCounters>();
     P.aov_albedo = c->aov_albedo.as<float4>(); P.aov_normal = c->aov_normal.as<float4>();
     return P;
+}
+
+// the shade stages of one bounce, in stream order
+template <int INTEG>
+static int launch_shade_t(hj_ctx* c, uint32_t grid, cudaStream_t ps, const FrameK& F, const WfPtrs& P, int cur, int depth, uint32_t s0) {
+    int n = 4;
+    k_surface<INTEG><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+    if (INTEG != HJ_INTEGRATOR_PT && c->S.n_lights >= 1) { k_nee<INTEG><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, s0); n++; }
+    k_sample<INTEG, HJ_CLS_DISNEY><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+    k_sample<INTEG, HJ_CLS_GGX><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+    k_sample<INTEG, HJ_CLS_GLASS><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+    return n;
+}
+static int launch_shade(hj_ctx* c, int integrator, uint32_t grid, cudaStream_t ps, const FrameK& F, const WfPtrs& P, int cur, int depth, uint32_t s0) {
+    if (integrator == HJ_INTEGRATOR_PT) return launch_shade_t<HJ_INTEGRATOR_PT>(c, grid, ps, F, P, cur, depth, s0);
+    if (integrator == HJ_INTEGRATOR_NEE) return launch_shade_t<HJ_INTEGRATOR_NEE>(c, grid, ps, F, P, cur, depth, s0);
+    return launch_shade_t<HJ_INTEGRATOR_MIS>(c, grid, ps, F, P, cur, depth, s0);
 }
 
 int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
@@ -611,11 +631,9 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
             else k_trace<0, false><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
             mark_end(ps);
             mark_begin(1, ps);
-            if (fp->integrator == HJ_INTEGRATOR_PT) k_shade<HJ_INTEGRATOR_PT><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
-            else if (fp->integrator == HJ_INTEGRATOR_NEE) k_shade<HJ_INTEGRATOR_NEE><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
-            else k_shade<HJ_INTEGRATOR_MIS><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+            launches += launch_shade(c, fp->integrator, grid, ps, F, P, cur, depth, s0);
             mark_end(ps);
-            launches += 2;
+            launches += 1;
             if (fp->integrator != HJ_INTEGRATOR_PT) {
                 mark_begin(0, ps);
                 if (count) k_trace<1, true><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
