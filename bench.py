@@ -209,8 +209,9 @@ def gpu_arm(args, rank, world, local_rank):
                data="synthetic", impl="ours",
                config=dict(workload=desc, triangles=scene.n_triangles, width=W, height=H, spp_per_gpu=spp, max_depth=cfg["max_depth"],
                            integrator="MIS", parallelism="sample slices, replicated scene, NCCL all-reduce of accum" if world > 1 else "single GPU",
-                           l2_policy="inputs larger than L2 (126 MB): 8 pipelines x 2M paths x ~250 B of path state rewritten every bounce "
-                                     "+ %.0f MB of BVH nodes and triangles" % ((r.stats()["bvh_nodes"] * 80 + scene.n_triangles * 48) / 1e6),
+                           l2_policy="inputs larger than L2 (126 MB): %d passes of %.1f M paths in flight x ~280 B of path state rewritten every "
+                                     "bounce + %.0f MB of BVH nodes and triangles" % (min(8, r.stats()["passes"]), spp * W * H / max(1, r.stats()["passes"]) / 1e6,
+                                                                                     (r.stats()["bvh_nodes"] * 80 + scene.n_triangles * 48) / 1e6),
                            timing="CUDA events on the context stream (N=1) / barrier-bracketed wall clock incl. all-reduce, max over ranks (N>1)"),
                spp_per_s=round(spp * world * args.steps / t_all, 3), rays_per_step=rays_all // args.steps,
                gpu_launches=launches_all, accel_build_ms=round(accel_ms, 3), clocks=clk, wall_s=round(wall, 3))
@@ -244,7 +245,8 @@ def gpu_arm(args, rank, world, local_rank):
         # (share = sum of traversal launch durations / sum of all stage durations), and applied to the timed step.
         share = stt["ms_trace"] / max(stt["ms_trace"] + stt["ms_shade"], 1e-9)
         step_ms = 1e3 * t_all / args.steps
-        n_trace_launches = 3 * cfg["max_depth"] * max(1, -(-spp * W * H // (2 << 20)))
+        n_types = {abi.INTEGRATOR_PT: 1, abi.INTEGRATOR_NEE: 2, abi.INTEGRATOR_MIS: 3}[cfg["integrator"]]
+        n_trace_launches = n_types * cfg["max_depth"] * max(1, stt["passes"])
         ach = algo / (share * step_ms / 1e3) / 1e9
         ach_serial = algo / (stt["ms_trace"] / 1e3) / 1e9
         out["roofline"] = dict(bound="hbm", achieved=round(ach, 1), peak=peak, unit="GB/s", frac=round(ach / peak, 4), traffic=None,

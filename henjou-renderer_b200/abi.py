@@ -60,7 +60,7 @@ class hj_stats(C.Structure):
         ("nodes_fetched", C.c_uint64), ("tris_fetched", C.c_uint64), ("kernel_launches", C.c_uint64),
         ("ms_render", C.c_float), ("ms_trace", C.c_float), ("ms_shade", C.c_float), ("ms_accel", C.c_float),
         ("bvh_nodes", C.c_uint32), ("bvh_node_bytes", C.c_uint32),
-        ("bvh_depth", C.c_uint32), ("max_nodes_per_ray", C.c_uint32), ("max_tris_per_ray", C.c_uint32), ("reserved", C.c_uint32),
+        ("bvh_depth", C.c_uint32), ("max_nodes_per_ray", C.c_uint32), ("max_tris_per_ray", C.c_uint32), ("passes", C.c_uint32),
     ]
 
 

@@ -668,6 +668,7 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     c->fp = *fp; c->have_frame = true;
     c->stats.kernel_launches = launches;
     c->stats.paths = (uint64_t)ns * WH;
+    c->stats.passes = n_passes;
     return HJ_OK;
 }
 

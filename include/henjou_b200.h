@@ -150,7 +150,7 @@ typedef struct hj_stats {
     uint32_t bvh_depth;           /* levels of the 8-wide tree                                                  */
     uint32_t max_nodes_per_ray;   /* worst single ray of the last hj_render (only with "count_fetches")         */
     uint32_t max_tris_per_ray;
-    uint32_t reserved;
+    uint32_t passes;              /* wavefront passes of the last hj_render (each: max_depth x (1 extend + 1 shadow + 1 MIS) traversal launches) */
 } hj_stats;
 
 int hj_abi_version(void);
