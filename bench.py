@@ -215,20 +215,31 @@ def gpu_arm(args, rank, world, local_rank):
                            timing="CUDA events on the context stream (N=1) / barrier-bracketed wall clock incl. all-reduce, max over ranks (N>1)"),
                spp_per_s=round(spp * world * args.steps / t_all, 3), rays_per_step=rays_all // args.steps,
                gpu_launches=launches_all, accel_build_ms=round(accel_ms, 3), clocks=clk, wall_s=round(wall, 3))
+    # ---- e2e through the C ABI with host buffers, every rank: upload + BVH rebuild + render (+ all-reduce) + read-back
+    h2d = scene.vertices.nbytes + scene.normals.nbytes + scene.texcoords.nbytes + scene.indices.nbytes + scene.material_ids.nbytes + \
+        scene.prim_offsets.nbytes + xf.nbytes + inv.nbytes + (scene.lut.nbytes if scene.lut is not None else 0) + scene.ibl.nbytes
+    d2h = W * H * 16 + W * H * 4
+    color = np.empty((H, W, 4), np.float32); rgba = np.empty((H, W, 4), np.uint8)
+    barrier()
+    e_rays, t0 = 0, time.perf_counter()
+    for _ in range(args.steps):
+        r.upload(scene); r.build_accel(xf, inv); r.render(fp, sync=False)
+        if world > 1:
+            r.comm_reduce()
+        r.sync()
+        r.readback(abi.AOV_COLOR, color); r.readback(abi.AOV_RGBA8, rgba)
+        st = r.stats(); e_rays += st["rays_extend"] + st["rays_shadow"]
+    barrier()
+    e_t = time.perf_counter() - t0
+    if world > 1:
+        import torch
+        tt = torch.tensor([e_t, float(e_rays)], dtype=torch.float64, device="cuda")
+        tmax = tt.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = tt.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        e_t, e_rays = float(tmax[0]), int(tsum[1])
+    out["e2e"] = dict(value=round(e_rays / e_t / 1e6, 2), unit="Mrays/s", h2d_bytes_per_step=int(h2d) * world, d2h_bytes_per_step=int(d2h) * world,
+                      ms_per_step=round(1e3 * e_t / args.steps, 3), checksum=float(color[..., :3].mean()))
     if rank == 0 and world == 1:
-        # ---- e2e through the C ABI with host buffers
-        h2d = scene.vertices.nbytes + scene.normals.nbytes + scene.texcoords.nbytes + scene.indices.nbytes + scene.material_ids.nbytes + \
-            scene.prim_offsets.nbytes + xf.nbytes + inv.nbytes + (scene.lut.nbytes if scene.lut is not None else 0) + scene.ibl.nbytes
-        d2h = W * H * 16 + W * H * 4
-        color = np.empty((H, W, 4), np.float32); rgba = np.empty((H, W, 4), np.uint8)
-        e_rays, t0 = 0, time.perf_counter()
-        for _ in range(args.steps):
-            r.upload(scene); r.build_accel(xf, inv); r.render(fp)
-            r.readback(abi.AOV_COLOR, color); r.readback(abi.AOV_RGBA8, rgba)
-            st = r.stats(); e_rays += st["rays_extend"] + st["rays_shadow"]
-        e_t = time.perf_counter() - t0
-        out["e2e"] = dict(value=round(e_rays / e_t / 1e6, 2), unit="Mrays/s", h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h),
-                          ms_per_step=round(1e3 * e_t / args.steps, 3), checksum=float(color[..., :3].mean()))
         # ---- roofline of the traversal kernels: bytes from a counters pass, time from an event-pair pass
         r.set_option("count_fetches", 1); r.render(fp); sc = r.stats(); r.set_option("count_fetches", 0)
         r.set_option("time_stages", 1); r.render(fp); stt = r.stats(); r.set_option("time_stages", 0)
