@@ -8,7 +8,7 @@
 //   radix sort     hand-written LSD radix sort, 8 bits per pass, (u64 key, u32 value) pairs
 //   k_karras       binary radix tree (Karras 2012)
 //   k_fit          bottom-up AABB fit
-//   k_collapse     level-by-level collapse to 8-wide nodes with 8-bit quantised child boxes (80 B / node)
+//   k_collapse     level-by-level collapse to 8-wide nodes with 8-bit quantised child boxes (112 B / node)
 #include "hj_ctx.h"
 #include "hj_trace.cuh"
 
@@ -428,12 +428,18 @@ __global__ void k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32
     const uint32_t tri_base = n_tri ? atomicAdd(&a.counters[1], n_tri) : 0u;
     // write the node
     auto pack4 = [](const uint32_t* v) { return v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24); };
-    uint4* N = a.nodes + 5 * (size_t)work.y;
+    uint4* N = a.nodes + HJ_NODE_QUADS * (size_t)work.y;
     N[0] = make_uint4(__float_as_uint(lo[0]), __float_as_uint(lo[1]), __float_as_uint(lo[2]), eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24));
-    N[1] = make_uint4(child_base, tri_base, pack4(meta), pack4(meta + 4));
+    // child masks: where a hit of slot s lands in the traversal's 32-bit hit word (bits 0..23 triangles of this node,
+    // bit 24+s inner child in slot s; the ray-octant permutation of the inner bits is applied by the traversal)
+    uint32_t cm[8];
+    for (int s = 0; s < 8; s++) cm[s] = (imask & (1u << s)) ? (1u << (24 + s)) : ((meta[s] >> 5) << (meta[s] & 31u));
+    N[1] = make_uint4(child_base, tri_base, cm[0], cm[1]);
     N[2] = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
     N[3] = make_uint4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
     N[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
+    N[5] = make_uint4(cm[2], cm[3], cm[4], cm[5]);
+    N[6] = make_uint4(cm[6], cm[7], pack4(meta), pack4(meta + 4));
     // children: queue the internal ones (contiguous, in slot order), copy the triangles of the leaves
     const uint32_t qbase = n_int ? atomicAdd(&a.counters[2], n_int) : 0u;
     uint32_t r = 0;
@@ -532,7 +538,7 @@ int hj_bvh_build(hj_ctx* c, int mode) {
     k_fit<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.vals.as<uint32_t>(), (int)n, B.left.as<uint32_t>(), B.right.as<uint32_t>(), B.parent.as<uint32_t>(),
                                         B.flags.as<uint32_t>(), B.blo.as<float4>(), B.bhi.as<float4>());
     // collapse, level by level
-    HJ_CUDA(c, B.nodes.reserve((size_t)n * 80)); HJ_CUDA(c, B.btris.reserve(3 * (size_t)n * sizeof(float4)));
+    HJ_CUDA(c, B.nodes.reserve((size_t)n * 16 * HJ_NODE_QUADS)); HJ_CUDA(c, B.btris.reserve(3 * (size_t)n * sizeof(float4)));
     HJ_CUDA(c, B.queue_a.reserve((size_t)n * sizeof(uint2))); HJ_CUDA(c, B.queue_b.reserve((size_t)n * sizeof(uint2)));
     HJ_CUDA(c, B.counters.reserve(4 * sizeof(uint32_t)));
     const uint32_t init_counters[4] = {1u, 0u, 0u, 0u};
@@ -565,6 +571,6 @@ int hj_bvh_build(hj_ctx* c, int mode) {
     }
     B.n_nodes = cnt[0]; B.depth = depth;
     c->S.nodes = B.nodes.as<uint4>(); c->S.btris = B.btris.as<float4>();
-    c->stats.ms_accel = ms; c->stats.bvh_nodes = B.n_nodes; c->stats.bvh_node_bytes = 80; c->stats.bvh_depth = depth;
+    c->stats.ms_accel = ms; c->stats.bvh_nodes = B.n_nodes; c->stats.bvh_node_bytes = 16 * HJ_NODE_QUADS; c->stats.bvh_depth = depth;
     return HJ_OK;
 }

@@ -2,15 +2,17 @@
 // optixTrace calls (/root/reference/include/kernel/rt.h:25 TraceOcculution, :53 RayTrace), which run on RT
 // cores inside the closed-source OptiX runtime. B200 has no RT cores: this is plain sm_100a CUDA.
 //
-// Node (80 B = five 16-byte loads; built by hj_bvh.cu):
+// Node (112 B = seven 16-byte words; built by hj_bvh.cu):
 //   q0: origin.xyz (float bits) | ex | ey<<8 | ez<<16 | imask<<24      (e* = biased float exponents of the grid step)
-//   q1: child_base (first internal child node), tri_base (first triangle of this node's leaves), meta[0..3], meta[4..7]
-//       meta[s] = (unary count << 5) | offset   leaf slot: 1..3 triangles at tri_base+offset (count bits 001/011/111)
-//               = (1 << 5) | (24 + s)           internal child in slot s (child node = child_base + popc(imask below s))
-//               = 0                              empty slot
-//       so `(meta >> 5) << (meta & 31)` drops a child's hit straight into a 32-bit mask: bits 0..23 = triangles
-//       of this node, bits 24..31 = internal children (Ylitie, Karras, Laine 2017)
+//   q1: child_base (first internal child node), tri_base (first triangle of this node's leaves), cm[0], cm[1]
 //   q2: qlo.x[0..7] qlo.y[0..7]   q3: qlo.z[0..7] qhi.x[0..7]   q4: qhi.y[0..7] qhi.z[0..7]      (8-bit grid coordinates)
+//   q5: cm[2..5]   q6: cm[6], cm[7], meta[0..3], meta[4..7]
+//       cm[s] = child mask of slot s: ((1 << count) - 1) << offset  leaf with 1..3 triangles at tri_base + offset
+//                                     1 << (24 + s)                  internal child (node = child_base + popc(imask below s))
+//                                     0                              empty slot
+//       so a hit ORs cm[s] into a 32-bit word: bits 0..23 = triangles of this node, bits 24..31 = internal children
+//       (the hit word of Ylitie, Karras, Laine 2017, precomputed per child instead of shifted together per visit).
+//       meta[s] = (unary count << 5) | offset: the builder's compact form of the same, kept for tools.
 // Child slots are assigned at build time by octant (slot bit k set = child on the + side of axis k), so
 // `slot ^ ray_octant` orders children front to back without sorting (Ylitie et al. 2017).
 //
@@ -22,9 +24,10 @@
 
 #define HJ_STACK 96          // local-memory part of the traversal stack
 #ifndef HJ_SSTACK
-#define HJ_SSTACK 12         // shared-memory part (entries per thread)
+#define HJ_SSTACK 8          // shared-memory part (entries per thread); what the blocks do not take stays L1 (ss12 -> ss8: +2 %)
 #endif
 #define HJ_TRACE_THREADS 128 // block size of every kernel that traverses
+#define HJ_NODE_QUADS 7      // 16-byte words per node (112 B)
 
 struct RayPrep {
     float3 o;
@@ -75,17 +78,22 @@ HJ_DI bool tri_test(const RayPrep& r, const float3& p0, const float3& p1, const 
 
 struct Hit { float t, b1, b2; uint32_t prim; };   // prim == 0xffffffff: miss
 
-// Intersects the 8 quantised child boxes of one 80-byte node with a ray: inner-child hits (bits 24..31, slot XOR octant
-// so that the highest bit is the nearest child) go to ng, triangle hits (bits 0..23, relative to tri_base) to tg.
 // k4b = bits of 2^23, which must sit in a REGISTER: PRMT takes one immediate, and that has to be the byte selector
 // (r01-g SASS: with a literal 2^23 ptxas kept the four selectors in registers instead, 45 extra moves per node).
 static __constant__ uint32_t c_two23 = 0x4B000000u;
 HJ_DI uint32_t load_two23() { return *(const volatile uint32_t*)&c_two23; }
 
+// Intersects the 8 quantised child boxes of one 112-byte node with a ray. A hit of slot s ORs the node's precomputed
+// child mask cm[s] into a 32-bit word: bits 0..23 triangles (relative to tri_base), bit 24+s inner child s. The inner
+// bits are then permuted by the ray octant (bit 24 + (s ^ oct_inv), so that the highest bit is the nearest child) with
+// one lookup in a 2 KB shared-memory table. r01-p SASS had the masks assembled from 8 meta bytes with ~53 ALU-pipe
+// instructions (extract, shift, select) per node; the ALU pipe (PRMT, FMNMX, SHF, LOP3, SEL at one warp instruction
+// per 2 cycles) is what bounds the node test, so those moved into the node: 80 -> 112 B, -40 ALU instructions.
 HJ_DI void node_boxes(const uint4* __restrict__ nodes, uint32_t node, const float3& o, const float3& idir, uint32_t oct,
-                      float tmin, float tcur, uint32_t k4b, uint2& ng, uint2& tg) {
-    const uint4* N = nodes + 5 * (size_t)node;
-    const uint4 q0 = __ldg(N), q1 = __ldg(N + 1), q2 = __ldg(N + 2), q3 = __ldg(N + 3), q4 = __ldg(N + 4);
+                      float tmin, float tcur, uint32_t k4b, const uint8_t* perm_row, uint2& ng, uint2& tg) {
+    const uint4* N = nodes + HJ_NODE_QUADS * (size_t)node;
+    const uint4 q0 = __ldg(N), q1 = __ldg(N + 1), q2 = __ldg(N + 2), q3 = __ldg(N + 3), q4 = __ldg(N + 4), q5 = __ldg(N + 5);
+    const uint2 q6 = __ldg((const uint2*)(N + 6));
     const float sx = __uint_as_float((q0.w & 0xffu) << 23), sy = __uint_as_float(((q0.w >> 8) & 0xffu) << 23),
                 sz = __uint_as_float(((q0.w >> 16) & 0xffu) << 23);
     const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
@@ -100,18 +108,12 @@ HJ_DI void node_boxes(const uint4* __restrict__ nodes, uint32_t node, const floa
     const float oxn = (ox - slack - fabsf(ax)) - bx, oyn = (oy - slack - fabsf(ay)) - by, ozn = (oz - slack - fabsf(az)) - bz;
     const float oxf = (ox + slack + fabsf(ax)) - bx, oyf = (oy + slack + fabsf(ay)) - by, ozf = (oz + slack + fabsf(az)) - bz;
     const bool nx = (oct & 1u) != 0, ny = (oct & 2u) != 0, nz = (oct & 4u) != 0;
-    const uint32_t oct_inv4 = (oct ^ 7u) * 0x01010101u;
+    const uint32_t cm[8] = {q1.z, q1.w, q5.x, q5.y, q5.z, q5.w, q6.x, q6.y};
     uint32_t hitmask = 0;
 #pragma unroll
     for (int h = 0; h < 2; h++) {
         const uint32_t lox = h ? q2.y : q2.x, loy = h ? q2.w : q2.z, loz = h ? q3.y : q3.x;
         const uint32_t hix = h ? q3.w : q3.z, hiy = h ? q4.y : q4.x, hiz = h ? q4.w : q4.z;
-        const uint32_t meta4 = h ? q1.w : q1.z;
-        // four metas at once: inner children (bit index 24..31 = 0b11xxx) get their slot XORed with the octant
-        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        const uint32_t inner_mask4 = (is_inner4 >> 4) * 0x07u;
-        const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1f1f1f1fu;
-        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
         const uint32_t nearx = nx ? hix : lox, farx = nx ? lox : hix;
         const uint32_t neary = ny ? hiy : loy, fary = ny ? loy : hiy;
         const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
@@ -126,14 +128,24 @@ HJ_DI void node_boxes(const uint4* __restrict__ nodes, uint32_t node, const floa
             const float tfz = __fmaf_rn(__uint_as_float(__byte_perm(farz, k4b, sel)), az, ozf);
             const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
             const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tcur));
-            const uint32_t bits = (child_bits4 >> (8 * j)) & 0xffu, idx = (bit_index4 >> (8 * j)) & 0xffu;
-            if (tn <= tf) hitmask |= bits << idx;      // empty slots have meta = 0
+            if (tn <= tf) hitmask |= cm[4 * h + j];      // empty slots have cm = 0
         }
     }
-    ng = make_uint2(q1.x, (hitmask & 0xff000000u) | (q0.w >> 24));
+    ng = make_uint2(q1.x, ((uint32_t)perm_row[hitmask >> 24] << 24) | (q0.w >> 24));
     tg = make_uint2(q1.y, hitmask & 0x00ffffffu);
 }
 
+// perm[o][x]: bit s of x moved to bit s ^ o (o = ray octant ^ 7); filled by every traversal kernel at its start
+HJ_DI void fill_octant_perm(uint8_t (*perm)[256]) {
+    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) {
+        const uint32_t o = i >> 8, x = i & 255u;
+        uint32_t y = 0;
+#pragma unroll
+        for (uint32_t s = 0; s < 8u; s++) if (x & (1u << s)) y |= 1u << (s ^ o);
+        perm[o][x] = (uint8_t)y;
+    }
+    __syncthreads();
+}
 
 // ------------------------------------------------------------------------------------------------------------------
 // Warp-cooperative traversal (the loop every traversal kernel runs).
@@ -147,6 +159,13 @@ HJ_DI void node_boxes(const uint4* __restrict__ nodes, uint32_t node, const floa
 //   * a lane is finished when its node walk is done AND every pair it queued has been tested (ticket <= head);
 //   * rays are fetched dynamically: once REFILL_MIN lanes are idle the warp takes that many queue entries with one
 //     warp-aggregated atomicAdd.
+#ifndef HJ_PREFETCH
+#define HJ_PREFETCH 0        // 1 / 2: prefetch the next node into L1 / L2 right after a node test
+#endif
+#ifndef HJ_RECRING
+#define HJ_RECRING 1        // 1: ring of leaf records expanded at test time; 0: ring of (owner, triangle) pairs
+#endif
+#define HJ_RCAP 64           // records per warp: at most 32 new per node phase + fewer than 32 left over
 #ifndef HJ_QCAP
 #define HJ_QCAP 128          // ring entries per warp (power of two, >= 32 + 24)
 #endif
@@ -168,7 +187,12 @@ struct TraceShared {
     uint32_t ray[9][HJ_TRACE_THREADS];              // ox oy oz Sx Sy Sz (kx | ky<<2 | kz<<4) tmin tmax
     unsigned long long key[HJ_TRACE_THREADS];       // best hit: t bits << 32 | prim (miss: tmax bits << 32 | 0xffffffff)
     float2 bary[HJ_TRACE_THREADS];                  // barycentrics of the best hit
+    uint8_t perm[8][256];                           // octant permutation of the inner-child hit bits (fill_octant_perm)
+#if HJ_RECRING
+    uint2 rring[HJ_TRACE_THREADS / 32][HJ_RCAP];    // pending leaf records: first triangle (leaf order), hit bits | owner lane << 24
+#else
     uint32_t ring[HJ_TRACE_THREADS / 32][HJ_QCAP];  // pending pairs: owner lane | triangle (leaf order) << 5
+#endif
 };
 
 // IO: uint32_t count; bool load(idx, o, d, tmin, tmax) (false: empty entry); void finish(const Hit&)
@@ -178,7 +202,12 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                            unsigned long long* diag = nullptr) {
     const uint32_t FULL = 0xffffffffu;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, wbase = tid & ~31u;
+#if HJ_RECRING
+    uint2* rring = sh.rring[tid >> 5];
+    uint32_t npairs = 0;                            // warp-uniform: triangle tests pending in the ring
+#else
     uint32_t* ring = sh.ring[tid >> 5];
+#endif
     uint2* sstack = sh.stack + tid;
     uint32_t head = 0, tail = 0;                    // warp-uniform absolute ring positions
     uint32_t ticket = 0;                            // ring position after this lane's last queued pair
@@ -187,6 +216,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
     bool active = false, exhausted = false;
     uint32_t nn0 = 0, own_tris = 0;
     const uint32_t k4b = load_two23();
+    fill_octant_perm(sh.perm);
     uint32_t d_ph = 0, d_act = 0, d_walk = 0, d_wait = 0, d_hold = 0, d_bat = 0, d_blanes = 0;
     while (true) {
         // ---- lanes whose walk is over and whose queued pairs are all tested hand their result over (once per burst,
@@ -238,10 +268,105 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                     if (ng.y > 0x00ffffffu) { if (sp < HJ_SSTACK) sstack[sp * HJ_TRACE_THREADS] = ng; else l_stack[sp - HJ_SSTACK] = ng; sp++; }
                     if (COUNT) n_nodes++;
                     const float tcur = __uint_as_float((uint32_t)(sh.key[tid] >> 32));
-                    node_boxes(S.nodes, node, o, idir, oct, tmin, tcur, k4b, ng, tg);
+                    node_boxes(S.nodes, node, o, idir, oct, tmin, tcur, k4b, sh.perm[oct ^ 7u], ng, tg);
                     did = true;
+#if HJ_PREFETCH
+                    {   // the node this lane visits next is known now: start its fetch before the queueing / triangle work
+                        uint2 nx = ng;
+                        if (nx.y <= 0x00ffffffu && sp > 0 && sp <= HJ_SSTACK) nx = sstack[(sp - 1) * HJ_TRACE_THREADS];
+                        if (nx.y > 0x00ffffffu) {
+                            const uint32_t k2 = 31u - (uint32_t)__clz(nx.y), slot2 = (k2 - 24u) ^ (oct ^ 7u);
+                            const char* p = (const char*)(S.nodes + HJ_NODE_QUADS * (size_t)(nx.x + __popc(nx.y & 0xffu & ((1u << slot2) - 1u))));
+#if HJ_PREFETCH == 1
+                            asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); asm volatile("prefetch.global.L1 [%0];" :: "l"(p + 96));
+#else
+                            asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); asm volatile("prefetch.global.L2 [%0];" :: "l"(p + 96));
+#endif
+                        }
+                    }
+#endif
                 }
             }
+#if HJ_RECRING
+            // ---- queue the leaf hits: one record (first triangle, hit bits | owner lane << 24) per lane and node visit,
+            //      placed with a ballot prefix; the warp expands records into (owner, triangle) pairs when it tests them
+            const uint32_t cnt = active ? (uint32_t)__popc(tg.y) : 0u;
+            const uint32_t has = __ballot_sync(FULL, cnt != 0u);
+            if (has) {
+                if (cnt != 0u) {
+                    const uint32_t pos = tail + (uint32_t)__popc(has & ((1u << lane) - 1u));
+                    rring[pos & (HJ_RCAP - 1)] = make_uint2(tg.x, tg.y | (lane << 24));
+                    tg.y = 0u; ticket = pos + 1u; if (COUNT) own_tris += cnt;
+                }
+                tail += (uint32_t)__popc(has);
+                npairs += __reduce_add_sync(FULL, cnt);
+                __syncwarp();
+            }
+            // ---- triangle phase: 32 pairs at a time, one per lane
+            const bool walked = active && ng.y <= 0x00ffffffu && sp == 0;
+            const uint32_t waiting = __ballot_sync(FULL, walked && (int32_t)(head - ticket) < 0);
+            const uint32_t nwork = (uint32_t)__popc(__ballot_sync(FULL, did));
+            if (COUNT && diag) {       // lane-state census per node phase: phases, active, walking, waiting
+                const uint32_t na = __popc(__ballot_sync(FULL, active));
+                if (lane == 0) { d_ph++; d_act += na; d_walk += nwork; d_wait += __popc(waiting); }
+            }
+            uint32_t thr = nwork * TRI_K; if (thr > 32u) thr = 32u; if (thr < 1u) thr = 1u;
+            if (__popc(waiting) >= WAIT_MAX) thr = 1u;
+            while (npairs >= thr) {
+                // the first (up to) 32 records, one per lane; an exclusive prefix sum of their triangle counts tells which
+                // records are consumed whole (incl <= 32) and which one in part
+                const uint32_t nrec = tail - head;
+                uint2 rec = make_uint2(0u, 0u);
+                if (lane < nrec) rec = rring[(head + lane) & (HJ_RCAP - 1)];
+                const uint32_t c = (uint32_t)__popc(rec.y & 0x00ffffffu);
+                uint32_t incl = c;
+#pragma unroll
+                for (int dlt = 1; dlt < 32; dlt <<= 1) { const uint32_t v = __shfl_up_sync(FULL, incl, dlt); if ((int)lane >= dlt) incl += v; }
+                const uint32_t excl = incl - c;
+                const uint32_t starts = __reduce_or_sync(FULL, (c != 0u && excl < 32u) ? (1u << excl) : 0u);
+                uint32_t nb = __shfl_sync(FULL, incl, 31); if (nb > 32u) nb = 32u;
+                // pair number `lane` belongs to the record whose start flag is the last one at or below bit `lane`
+                const uint32_t k = (uint32_t)__popc(starts & (0xffffffffu >> (31u - lane))) - 1u;
+                const uint32_t kbase = __shfl_sync(FULL, rec.x, (int)(k & 31u)), kmask = __shfl_sync(FULL, rec.y, (int)(k & 31u)),
+                               kexcl = __shfl_sync(FULL, excl, (int)(k & 31u));
+                bool hit = false; unsigned long long key = 0; uint32_t ow = 0; float b1 = 0.0f, b2 = 0.0f;
+                if (lane < nb) {
+                    uint32_t m = kmask & 0x00ffffffu;
+                    for (uint32_t i = lane - kexcl; i > 0u; i--) m &= m - 1u;      // records are consumed from their lowest bit
+                    const uint32_t tri = kbase + (uint32_t)__ffs((int)m) - 1u;
+                    ow = wbase + (kmask >> 24);
+                    if (!ANY || (uint32_t)sh.key[ow] == 0xffffffffu) {
+                        const float4* T = S.btris + 3 * (size_t)tri;
+                        const float4 v0 = __ldg(T), v1 = __ldg(T + 1), v2 = __ldg(T + 2);
+                        if (COUNT) n_tris++;
+                        RayPrep r;
+                        r.o = f3(__uint_as_float(sh.ray[0][ow]), __uint_as_float(sh.ray[1][ow]), __uint_as_float(sh.ray[2][ow]));
+                        r.Sx = __uint_as_float(sh.ray[3][ow]); r.Sy = __uint_as_float(sh.ray[4][ow]); r.Sz = __uint_as_float(sh.ray[5][ow]);
+                        const uint32_t kp = sh.ray[6][ow];
+                        r.kx = (int)(kp & 3u); r.ky = (int)((kp >> 2) & 3u); r.kz = (int)(kp >> 4);
+                        float t;
+                        if (tri_test(r, f3(v0), f3(v1), f3(v2), __uint_as_float(sh.ray[7][ow]), __uint_as_float(sh.ray[8][ow]), t, b1, b2)) {
+                            hit = true;
+                            key = ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)__float_as_uint(v0.w);
+                            atomicMin(&sh.key[ow], key);
+                        }
+                    }
+                }
+                // the record cut by the batch keeps its untested (higher) bits; whole records leave the ring
+                if (lane < nrec && excl < 32u && incl > 32u) {
+                    uint32_t m = rec.y & 0x00ffffffu;
+                    for (uint32_t i = 32u - excl; i > 0u; i--) m &= m - 1u;
+                    rring[(head + lane) & (HJ_RCAP - 1)].y = m | (rec.y & 0xff000000u);
+                }
+                head += (uint32_t)__popc(__ballot_sync(FULL, lane < nrec && incl <= 32u));
+                npairs -= nb;
+                __syncwarp();
+                if (hit && sh.key[ow] == key) sh.bary[ow] = make_float2(b1, b2);
+                __syncwarp();
+                if (COUNT && diag && lane == 0) { d_bat++; d_blanes += nb; }
+                thr = 32u;                                         // after a forced partial batch only full ones
+            }
+#else
             // ---- queue the triangle hits: warp prefix sum of the counts, lanes that fit write (owner, triangle) pairs
             const uint32_t cnt = active ? (uint32_t)__popc(tg.y) : 0u;
             if (__any_sync(FULL, cnt != 0u)) {
@@ -301,6 +426,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                 if (COUNT && diag && lane == 0) { d_bat++; d_blanes += nb; }
                 thr = 32u;                                         // after a forced partial batch only full ones
             }
+#endif
             // ---- any hit ends an occlusion ray
             if (ANY && active && (uint32_t)sh.key[tid] != 0xffffffffu) { ng.y = 0u; tg.y = 0u; sp = 0; }
         }
