@@ -10,7 +10,7 @@ A step = one whole frame (all pixels x all samples of this rank's slice) through
   e2e     : the same metric through the C ABI with HOST buffers, every step: hj_scene_upload (geometry H2D) +
             hj_accel_build (transforms H2D, BVH rebuild ≙ updateIASMatrix) + hj_render + hj_readback of the colour
             AOV and the RGBA8 image (D2H), wall clock.
-  roofline: traversal kernels (k_extend + k_shadow + k_mis): algorithmic bytes = 80 B x nodes fetched + 48 B x
+  roofline: traversal kernels (k_trace<0|1|2>): algorithmic bytes = 112 B x nodes fetched + 48 B x
             triangles fetched (counters-enabled pass) / their summed launch durations (event pairs, separate pass).
   cpu_baseline: the reference's own device headers compiled for the host (oracle/_ref, kind "reference") or the
             CPU restatement (kind "port"), all host cores, on a bounded sample (pixel rows x few spp) of the workload.
@@ -211,7 +211,7 @@ def gpu_arm(args, rank, world, local_rank):
                            integrator="MIS", parallelism="sample slices, replicated scene, NCCL all-reduce of accum" if world > 1 else "single GPU",
                            l2_policy="inputs larger than L2 (126 MB): %d passes of %.1f M paths in flight x ~280 B of path state rewritten every "
                                      "bounce + %.0f MB of BVH nodes and triangles" % (min(8, r.stats()["passes"]), spp * W * H / max(1, r.stats()["passes"]) / 1e6,
-                                                                                     (r.stats()["bvh_nodes"] * 80 + scene.n_triangles * 48) / 1e6),
+                                                                                     (r.stats()["bvh_nodes"] * r.stats()["bvh_node_bytes"] + scene.n_triangles * 48) / 1e6),
                            timing="CUDA events on the context stream (N=1) / barrier-bracketed wall clock incl. all-reduce, max over ranks (N>1)"),
                spp_per_s=round(spp * world * args.steps / t_all, 3), rays_per_step=rays_all // args.steps,
                gpu_launches=launches_all, accel_build_ms=round(accel_ms, 3), clocks=clk, wall_s=round(wall, 3))
@@ -243,7 +243,8 @@ def gpu_arm(args, rank, world, local_rank):
         # ---- roofline of the traversal kernels: bytes from a counters pass, time from an event-pair pass
         r.set_option("count_fetches", 1); r.render(fp); sc = r.stats(); r.set_option("count_fetches", 0)
         r.set_option("time_stages", 1); r.render(fp); stt = r.stats(); r.set_option("time_stages", 0)
-        algo = 80.0 * sc["nodes_fetched"] + 48.0 * sc["tris_fetched"]
+        node_bytes = float(sc["bvh_node_bytes"])          # 112: seven 16-byte words per 8-wide node
+        algo = node_bytes * sc["nodes_fetched"] + 48.0 * sc["tris_fetched"]
         nrays = sc["rays_extend"] + sc["rays_shadow"]
         peaks = {}
         try:

@@ -159,9 +159,6 @@ HJ_DI void fill_octant_perm(uint8_t (*perm)[256]) {
 //   * a lane is finished when its node walk is done AND every pair it queued has been tested (ticket <= head);
 //   * rays are fetched dynamically: once REFILL_MIN lanes are idle the warp takes that many queue entries with one
 //     warp-aggregated atomicAdd.
-#ifndef HJ_PREFETCH
-#define HJ_PREFETCH 0        // 1 / 2: prefetch the next node into L1 / L2 right after a node test
-#endif
 #ifndef HJ_RECRING
 #define HJ_RECRING 1        // 1: ring of leaf records expanded at test time; 0: ring of (owner, triangle) pairs
 #endif
@@ -270,21 +267,6 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                     const float tcur = __uint_as_float((uint32_t)(sh.key[tid] >> 32));
                     node_boxes(S.nodes, node, o, idir, oct, tmin, tcur, k4b, sh.perm[oct ^ 7u], ng, tg);
                     did = true;
-#if HJ_PREFETCH
-                    {   // the node this lane visits next is known now: start its fetch before the queueing / triangle work
-                        uint2 nx = ng;
-                        if (nx.y <= 0x00ffffffu && sp > 0 && sp <= HJ_SSTACK) nx = sstack[(sp - 1) * HJ_TRACE_THREADS];
-                        if (nx.y > 0x00ffffffu) {
-                            const uint32_t k2 = 31u - (uint32_t)__clz(nx.y), slot2 = (k2 - 24u) ^ (oct ^ 7u);
-                            const char* p = (const char*)(S.nodes + HJ_NODE_QUADS * (size_t)(nx.x + __popc(nx.y & 0xffu & ((1u << slot2) - 1u))));
-#if HJ_PREFETCH == 1
-                            asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); asm volatile("prefetch.global.L1 [%0];" :: "l"(p + 96));
-#else
-                            asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); asm volatile("prefetch.global.L2 [%0];" :: "l"(p + 96));
-#endif
-                        }
-                    }
-#endif
                 }
             }
 #if HJ_RECRING

@@ -147,6 +147,12 @@ HJ_DI float light_pdf_area(const DevScene& S, uint32_t prim) {
 #ifndef HJ_SHADE_MINB
 #define HJ_SHADE_MINB 6
 #endif
+#ifndef HJ_SURF_MINB
+#define HJ_SURF_MINB HJ_SHADE_MINB
+#endif
+#ifndef HJ_NEE_MINB
+#define HJ_NEE_MINB HJ_SHADE_MINB
+#endif
 #define HJ_CLS_DISNEY 0
 #define HJ_CLS_GGX 1
 #define HJ_CLS_GLASS 2
@@ -162,7 +168,7 @@ HJ_DI Surface load_surface(const WfPtrs& P, uint32_t slot) {
 }
 
 template <int INTEG>
-__global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_surface(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
+__global__ void __launch_bounds__(WF_THREADS, HJ_SURF_MINB) k_surface(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
     const uint32_t n = P.cnt->n_extend[cur];
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
@@ -205,7 +211,7 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_surface(DevScene 
 // light sampling + BSDF evaluation of the non-specular surfaces (rt.h:219-260 / 341-380). Specular surfaces evaluate to
 // zero (BSDFs.h:1006-1013), so their light sample contributes nothing and only moves the RNG counter (k_sample skips it).
 template <int INTEG>
-__global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_nee(DevScene S, FrameK F, WfPtrs P, uint32_t s0) {
+__global__ void __launch_bounds__(WF_THREADS, HJ_NEE_MINB) k_nee(DevScene S, FrameK F, WfPtrs P, uint32_t s0) {
     const uint32_t n = P.cnt->n_ns;
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
