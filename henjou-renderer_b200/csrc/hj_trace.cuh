@@ -151,21 +151,15 @@ HJ_DI void fill_octant_perm(uint8_t (*perm)[256]) {
 // Warp-cooperative traversal (the loop every traversal kernel runs).
 //
 // Lanes own rays and walk the node hierarchy; the triangle tests they generate are NOT run by the owning lane: every
-// (owner lane, triangle) pair goes into a per-warp ring in shared memory and the warp tests 32 pairs at a time, one per
-// lane, whoever owns them. The owner's ray (origin + watertight shear) and its current best hit live in shared memory;
+// lane with leaf hits puts one record into a per-warp ring in shared memory and the warp expands the records and tests
+// 32 (owner lane, triangle) pairs at a time, one per lane, whoever owns them. The owner's ray (origin + watertight shear) and its current best hit live in shared memory;
 // a tester merges a hit with one 64-bit atomicMin on the key (t bits << 32 | global primitive id) — exactly the
 // closest-hit rule (smaller t, ties -> lower id), so the result is still a pure function of (ray, scene). Lanes never
 // wait inside a triangle phase; r01-e measured 13-15 of 32 lanes per instruction with per-lane triangle tests.
 //   * a lane is finished when its node walk is done AND every pair it queued has been tested (ticket <= head);
 //   * rays are fetched dynamically: once REFILL_MIN lanes are idle the warp takes that many queue entries with one
 //     warp-aggregated atomicAdd.
-#ifndef HJ_RECRING
-#define HJ_RECRING 1        // 1: ring of leaf records expanded at test time; 0: ring of (owner, triangle) pairs
-#endif
 #define HJ_RCAP 64           // records per warp: at most 32 new per node phase + fewer than 32 left over
-#ifndef HJ_QCAP
-#define HJ_QCAP 128          // ring entries per warp (power of two, >= 32 + 24)
-#endif
 #ifndef REFILL_MIN
 #define REFILL_MIN 8         // idle lanes before a warp fetches new rays
 #endif
@@ -185,11 +179,7 @@ struct TraceShared {
     unsigned long long key[HJ_TRACE_THREADS];       // best hit: t bits << 32 | prim (miss: tmax bits << 32 | 0xffffffff)
     float2 bary[HJ_TRACE_THREADS];                  // barycentrics of the best hit
     uint8_t perm[8][256];                           // octant permutation of the inner-child hit bits (fill_octant_perm)
-#if HJ_RECRING
     uint2 rring[HJ_TRACE_THREADS / 32][HJ_RCAP];    // pending leaf records: first triangle (leaf order), hit bits | owner lane << 24
-#else
-    uint32_t ring[HJ_TRACE_THREADS / 32][HJ_QCAP];  // pending pairs: owner lane | triangle (leaf order) << 5
-#endif
 };
 
 // IO: uint32_t count; bool load(idx, o, d, tmin, tmax) (false: empty entry); void finish(const Hit&)
@@ -199,12 +189,8 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                            unsigned long long* diag = nullptr) {
     const uint32_t FULL = 0xffffffffu;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, wbase = tid & ~31u;
-#if HJ_RECRING
     uint2* rring = sh.rring[tid >> 5];
     uint32_t npairs = 0;                            // warp-uniform: triangle tests pending in the ring
-#else
-    uint32_t* ring = sh.ring[tid >> 5];
-#endif
     uint2* sstack = sh.stack + tid;
     uint32_t head = 0, tail = 0;                    // warp-uniform absolute ring positions
     uint32_t ticket = 0;                            // ring position after this lane's last queued pair
@@ -269,7 +255,6 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                     did = true;
                 }
             }
-#if HJ_RECRING
             // ---- queue the leaf hits: one record (first triangle, hit bits | owner lane << 24) per lane and node visit,
             //      placed with a ballot prefix; the warp expands records into (owner, triangle) pairs when it tests them
             const uint32_t cnt = active ? (uint32_t)__popc(tg.y) : 0u;
@@ -348,67 +333,6 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                 if (COUNT && diag && lane == 0) { d_bat++; d_blanes += nb; }
                 thr = 32u;                                         // after a forced partial batch only full ones
             }
-#else
-            // ---- queue the triangle hits: warp prefix sum of the counts, lanes that fit write (owner, triangle) pairs
-            const uint32_t cnt = active ? (uint32_t)__popc(tg.y) : 0u;
-            if (__any_sync(FULL, cnt != 0u)) {
-                uint32_t incl = cnt;
-#pragma unroll
-                for (int dlt = 1; dlt < 32; dlt <<= 1) { const uint32_t v = __shfl_up_sync(FULL, incl, dlt); if ((int)lane >= dlt) incl += v; }
-                const uint32_t room = HJ_QCAP - (tail - head);
-                const bool fit = incl <= room;                     // a prefix of the lanes
-                if (cnt != 0u && fit) {
-                    uint32_t m = tg.y, pos = tail + incl - cnt;
-                    while (m) {
-                        const uint32_t j = 31u - (uint32_t)__clz(m); m &= ~(1u << j);
-                        ring[pos++ & (HJ_QCAP - 1)] = lane | ((tg.x + j) << 5);
-                    }
-                    tg.y = 0u; ticket = pos; if (COUNT) own_tris += cnt;
-                }
-                tail += __reduce_max_sync(FULL, fit ? incl : 0u);
-                __syncwarp();
-            }
-            // ---- triangle phase: 32 pairs at a time, one per lane
-            const bool walked = active && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u;
-            const uint32_t waiting = __ballot_sync(FULL, walked && (int32_t)(head - ticket) < 0);
-            const uint32_t nwork = (uint32_t)__popc(__ballot_sync(FULL, did));
-            if (COUNT && diag) {       // lane-state census per node phase: phases, active, walking, waiting, holding triangles
-                const uint32_t na = __popc(__ballot_sync(FULL, active)), nh = __popc(__ballot_sync(FULL, active && tg.y != 0u));
-                if (lane == 0) { d_ph++; d_act += na; d_walk += nwork; d_wait += __popc(waiting); d_hold += nh; }
-            }
-            uint32_t thr = nwork * TRI_K; if (thr > 32u) thr = 32u; if (thr < 1u) thr = 1u;
-            if (__popc(waiting) >= WAIT_MAX) thr = 1u;
-            while (tail - head >= thr) {
-                uint32_t nb = tail - head; if (nb > 32u) nb = 32u;
-                bool hit = false; unsigned long long key = 0; uint32_t ow = 0; float b1 = 0.0f, b2 = 0.0f;
-                if (lane < nb) {
-                    const uint32_t e = ring[(head + lane) & (HJ_QCAP - 1)];
-                    ow = wbase + (e & 31u);
-                    if (!ANY || (uint32_t)sh.key[ow] == 0xffffffffu) {
-                        const float4* T = S.btris + 3 * (size_t)(e >> 5);
-                        const float4 v0 = __ldg(T), v1 = __ldg(T + 1), v2 = __ldg(T + 2);
-                        if (COUNT) n_tris++;
-                        RayPrep r;
-                        r.o = f3(__uint_as_float(sh.ray[0][ow]), __uint_as_float(sh.ray[1][ow]), __uint_as_float(sh.ray[2][ow]));
-                        r.Sx = __uint_as_float(sh.ray[3][ow]); r.Sy = __uint_as_float(sh.ray[4][ow]); r.Sz = __uint_as_float(sh.ray[5][ow]);
-                        const uint32_t kp = sh.ray[6][ow];
-                        r.kx = (int)(kp & 3u); r.ky = (int)((kp >> 2) & 3u); r.kz = (int)(kp >> 4);
-                        float t;
-                        if (tri_test(r, f3(v0), f3(v1), f3(v2), __uint_as_float(sh.ray[7][ow]), __uint_as_float(sh.ray[8][ow]), t, b1, b2)) {
-                            hit = true;
-                            key = ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)__float_as_uint(v0.w);
-                            atomicMin(&sh.key[ow], key);
-                        }
-                    }
-                }
-                __syncwarp();
-                if (hit && sh.key[ow] == key) sh.bary[ow] = make_float2(b1, b2);
-                __syncwarp();
-                head += nb;
-                if (COUNT && diag && lane == 0) { d_bat++; d_blanes += nb; }
-                thr = 32u;                                         // after a forced partial batch only full ones
-            }
-#endif
             // ---- any hit ends an occlusion ray
             if (ANY && active && (uint32_t)sh.key[tid] != 0xffffffffu) { ng.y = 0u; tg.y = 0u; sp = 0; }
         }
