@@ -227,7 +227,9 @@ __global__ void k_fit(const DevScene S, const uint32_t* __restrict__ sorted, int
 // clusters. Every round each cluster looks PLOC_RADIUS neighbours to either side for the partner that minimises the
 // surface area of the merged box; mutual nearest neighbours merge. Builds a much better tree than the Karras radix
 // tree over the same order (fewer node visits per ray, no pathological long rays through flat tessellated surfaces).
-#define PLOC_RADIUS 12
+#ifndef PLOC_RADIUS
+#define PLOC_RADIUS 8      // r01-u sweep on C2 (2..100): 6-8 give the fewest node visits and the shortest build
+#endif
 #define PLOC_THREADS 256
 
 __global__ void k_ploc_init(const DevScene S, const uint32_t* __restrict__ sorted, int n, uint32_t* cid, float4* clo, float4* chi, float4* blo, float4* bhi) {
