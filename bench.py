@@ -220,6 +220,10 @@ def gpu_arm(args, rank, world, local_rank):
         scene.prim_offsets.nbytes + xf.nbytes + inv.nbytes + (scene.lut.nbytes if scene.lut is not None else 0) + scene.ibl.nbytes
     d2h = W * H * 16 + W * H * 4
     color = np.empty((H, W, 4), np.float32); rgba = np.empty((H, W, 4), np.uint8)
+    # the host buffers are page-locked once (hj_host_pin), as a host that re-uploads every frame would do
+    pinned = [a for a in (scene.vertices, scene.normals, scene.texcoords, scene.indices, scene.material_ids, color, rgba)
+              if a.flags["C_CONTIGUOUS"]] if not args.pageable else []
+    r.pin(*pinned)
     barrier()
     e_rays, t0 = 0, time.perf_counter()
     for _ in range(args.steps):
@@ -238,7 +242,9 @@ def gpu_arm(args, rank, world, local_rank):
         tsum = tt.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         e_t, e_rays = float(tmax[0]), int(tsum[1])
     out["e2e"] = dict(value=round(e_rays / e_t / 1e6, 2), unit="Mrays/s", h2d_bytes_per_step=int(h2d) * world, d2h_bytes_per_step=int(d2h) * world,
-                      ms_per_step=round(1e3 * e_t / args.steps, 3), checksum=float(color[..., :3].mean()))
+                      ms_per_step=round(1e3 * e_t / args.steps, 3), checksum=float(color[..., :3].mean()),
+                      host_memory="pageable" if args.pageable else "pinned (hj_host_pin)")
+    r.unpin(*pinned)
     if rank == 0 and world == 1:
         # ---- roofline of the traversal kernels: bytes from a counters pass, time from an event-pair pass
         r.set_option("count_fetches", 1); r.render(fp); sc = r.stats(); r.set_option("count_fetches", 0)
@@ -309,6 +315,7 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--cpu-budget", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--pageable", action="store_true", help="e2e leg with pageable host buffers (no hj_host_pin)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":

@@ -273,6 +273,20 @@ int hj_readback(hj_ctx* c, int aov, void* dst, size_t bytes) {
     return HJ_OK;
 }
 
+int hj_host_pin(hj_ctx* c, void* ptr, size_t bytes) {
+    if (!c || !ptr || !bytes) return HJ_ERR_INVALID;
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    HJ_CUDA(c, cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return HJ_OK;
+}
+
+int hj_host_unpin(hj_ctx* c, void* ptr) {
+    if (!c || !ptr) return HJ_ERR_INVALID;
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    HJ_CUDA(c, cudaHostUnregister(ptr));
+    return HJ_OK;
+}
+
 void* hj_device_ptr(hj_ctx* c, int aov) {
     if (!c || !c->have_frame) return nullptr;
     void* p = nullptr; size_t b = 0;

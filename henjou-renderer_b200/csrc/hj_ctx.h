@@ -94,6 +94,7 @@ struct hj_ctx {
             char b_[512];                                                                          \
             snprintf(b_, sizeof b_, "%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
             (ctx)->err = b_;                                                                       \
+            (void)cudaGetLastError(); /* a recoverable error must not fail the next call's launch check */ \
             return (e_ == cudaErrorMemoryAllocation) ? HJ_ERR_OOM : HJ_ERR_CUDA;                   \
         }                                                                                          \
     } while (0)

@@ -46,6 +46,8 @@ def load_library():
     L.hj_finalize.argtypes = [vp]
     L.hj_get_stats.argtypes = [vp, C.POINTER(abi.hj_stats)]
     L.hj_trace.argtypes = [vp, abi.f32p, C.c_uint64, C.c_int, abi.u32p, abi.f32p]
+    L.hj_host_pin.argtypes = [vp, vp, C.c_size_t]
+    L.hj_host_unpin.argtypes = [vp, vp]
     L.hj_comm_unique_id.argtypes = [vp]
     L.hj_comm_init.argtypes = [vp, vp, C.c_int, C.c_int]
     L.hj_comm_reduce.argtypes = [vp]
@@ -103,6 +105,17 @@ class Renderer:
             out = np.empty(shape, dt)
         self._check(self.L.hj_readback(self.ctx, aov, out.ctypes.data_as(C.c_void_p), out.nbytes), "hj_readback")
         return out
+
+    def pin(self, *arrays):
+        """Page-locks numpy buffers handed to upload()/readback() (hj_host_pin); keep them alive until unpin()."""
+        for a in arrays:
+            if a is not None and a.nbytes:
+                self._check(self.L.hj_host_pin(self.ctx, a.ctypes.data_as(C.c_void_p), a.nbytes), "hj_host_pin")
+
+    def unpin(self, *arrays):
+        for a in arrays:
+            if a is not None and a.nbytes:
+                self._check(self.L.hj_host_unpin(self.ctx, a.ctypes.data_as(C.c_void_p)), "hj_host_unpin")
 
     def device_ptr(self, aov):
         return self.L.hj_device_ptr(self.ctx, aov)

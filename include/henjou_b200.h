@@ -182,6 +182,13 @@ int hj_sync(hj_ctx* ctx);
 /* Copies an AOV of the last rendered frame into caller memory; `bytes` must be the exact size. */
 int hj_readback(hj_ctx* ctx, int aov, void* dst, size_t bytes);
 
+/* Page-locks / releases caller memory (cudaHostRegister) so that hj_scene_upload / hj_readback DMA straight from / into it
+ * instead of going through the driver's staging copies; for hosts without the CUDA headers. The reference keeps its
+ * geometry in std::vector and copies it with cudaMemcpy (renderer.h:560-640, pageable): pinning is optional, the result
+ * is the same bytes. Pin once, reuse across frames, unpin before freeing the memory. */
+int hj_host_pin(hj_ctx* ctx, void* ptr, size_t bytes);
+int hj_host_unpin(hj_ctx* ctx, void* ptr);
+
 /* Device address of an AOV buffer (for torch.distributed / zero-copy consumers); NULL if absent. */
 void* hj_device_ptr(hj_ctx* ctx, int aov);
 

@@ -163,3 +163,21 @@ def test_error_paths(gpu, cornell):
     with pytest.raises(hj.HenjouError):
         r.render(bad)
     r.close()
+
+
+def test_pinned_host_buffers_give_the_same_frame(gpu, cornell):
+    """hj_host_pin / hj_host_unpin: page-locked caller memory changes the copy path, not a single byte of the result."""
+    fp = hj.frame_params(cornell, 64, 48, 2)
+    gpu.upload(cornell); gpu.build_accel(); gpu.render(fp)
+    want = gpu.readback(abi.AOV_COLOR).copy()
+    big = [cornell.vertices, cornell.normals, cornell.texcoords, cornell.indices, cornell.material_ids]
+    out = np.empty((48, 64, 4), np.float32)
+    gpu.pin(*big, out)
+    try:
+        gpu.upload(cornell); gpu.build_accel(); gpu.render(fp)
+        gpu.readback(abi.AOV_COLOR, out)
+    finally:
+        gpu.unpin(*big, out)
+    assert np.array_equal(out.view(np.uint32), want.view(np.uint32))
+    with pytest.raises(hj.HenjouError):
+        gpu.unpin(out)                                       # not pinned any more
