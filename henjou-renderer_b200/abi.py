@@ -4,7 +4,8 @@ import ctypes as C
 HJ_OK = 0
 INTEGRATOR_PT, INTEGRATOR_NEE, INTEGRATOR_MIS = 0, 1, 2
 TONEMAP_NONE, TONEMAP_ACES, TONEMAP_UCHIMURA = 0, 1, 2
-AOV_COLOR, AOV_ALBEDO, AOV_NORMAL, AOV_RGBA8, AOV_ACCUM, AOV_PATH_RADIANCE, AOV_PATH_IDS = range(7)
+AOV_COLOR, AOV_ALBEDO, AOV_NORMAL, AOV_RGBA8, AOV_ACCUM, AOV_PATH_RADIANCE, AOV_PATH_IDS, AOV_OUTPUT, AOV_OUTPUT_RGBA8 = range(9)
+POST_PASSTHROUGH, POST_DENOISE, POST_DENOISE_UPSCALE2X = 0, 1, 2
 ACCEL_BUILD, ACCEL_REFIT = 0, 1
 
 f32p = C.POINTER(C.c_float)
@@ -60,7 +61,8 @@ class hj_stats(C.Structure):
         ("nodes_fetched", C.c_uint64), ("tris_fetched", C.c_uint64), ("kernel_launches", C.c_uint64),
         ("ms_render", C.c_float), ("ms_trace", C.c_float), ("ms_shade", C.c_float), ("ms_accel", C.c_float),
         ("bvh_nodes", C.c_uint32), ("bvh_node_bytes", C.c_uint32),
-        ("bvh_depth", C.c_uint32), ("max_nodes_per_ray", C.c_uint32), ("max_tris_per_ray", C.c_uint32), ("passes", C.c_uint32),
+        ("bvh_depth", C.c_uint32), ("max_nodes_per_ray", C.c_uint32), ("max_tris_per_ray", C.c_uint32), ("ms_post", C.c_float), ("post_launches", C.c_uint32),
+        ("passes", C.c_uint32),
     ]
 
 
@@ -69,5 +71,5 @@ EXPORTS = [
     "hj_abi_version", "hj_create", "hj_destroy", "hj_last_error", "hj_set_option", "hj_scene_upload",
     "hj_accel_build", "hj_render", "hj_render_async", "hj_sync", "hj_readback", "hj_device_ptr",
     "hj_finalize", "hj_get_stats", "hj_comm_unique_id", "hj_comm_init", "hj_comm_reduce", "hj_trace",
-    "hj_host_pin", "hj_host_unpin",
+    "hj_host_pin", "hj_host_unpin", "hj_post",
 ]

@@ -65,7 +65,8 @@ void hj_destroy(hj_ctx* c) {
                       &c->bvh.right, &c->bvh.parent, &c->bvh.cnt, &c->bvh.flags, &c->bvh.p_cid[0], &c->bvh.p_cid[1], &c->bvh.p_lo[0], &c->bvh.p_lo[1],
                       &c->bvh.p_hi[0], &c->bvh.p_hi[1], &c->bvh.p_nn, &c->bvh.p_keep, &c->bvh.p_bcount, &c->bvh.bounds, &c->bvh.queue_a, &c->bvh.queue_b,
                       &c->bvh.counters, &c->bvh.nodes, &c->bvh.btris,
-                      &c->aov_color, &c->aov_albedo, &c->aov_normal, &c->aov_rgba8, &c->aov_accum, &c->aov_path_rad, &c->aov_path_ids};
+                      &c->aov_color, &c->aov_albedo, &c->aov_normal, &c->aov_rgba8, &c->aov_accum, &c->aov_path_rad, &c->aov_path_ids,
+                      &c->aov_output, &c->aov_output_rgba8, &c->post_tmp[0], &c->post_tmp[1]};
     for (DevBuf* b : bufs) b->release();
     for (WavefrontState& w : c->wf) {
         for (DevBuf* b : w.all) if (b) b->release();
@@ -73,6 +74,8 @@ void hj_destroy(hj_ctx* c) {
         if (w.ev_acc) cudaEventDestroy(w.ev_acc);
     }
     if (c->ev_frame) cudaEventDestroy(c->ev_frame);
+    if (c->ev_post0) cudaEventDestroy(c->ev_post0);
+    if (c->ev_post1) cudaEventDestroy(c->ev_post1);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
@@ -88,6 +91,14 @@ int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
     else if (!strcmp(key, "pipelines")) { HJ_REQUIRE(c, value >= 1 && value <= HJ_MAX_PIPES, HJ_ERR_INVALID, "hj_set_option: pipelines must be 1..8"); c->opt_pipelines = (int)value; }
     else if (!strcmp(key, "builder")) { HJ_REQUIRE(c, value == 0 || value == 1, HJ_ERR_INVALID, "hj_set_option: builder must be 0 (LBVH) or 1 (PLOC)"); c->opt_builder = (int)value; c->bvh.have_topology = false; }
     else if (!strcmp(key, "leaf_max")) { HJ_REQUIRE(c, value >= 1 && value <= 3, HJ_ERR_INVALID, "hj_set_option: leaf_max must be 1..3"); c->opt_leaf_max = (int)value; }
+    else if (!strcmp(key, "denoise_iterations")) { HJ_REQUIRE(c, value >= 0 && value <= 8, HJ_ERR_INVALID, "hj_set_option: denoise_iterations must be 0..8"); c->opt_denoise_iterations = (int)value; }
+    else if (!strncmp(key, "denoise_sigma_", 14)) {
+        HJ_REQUIRE(c, value >= 1 && value <= 1000000, HJ_ERR_INVALID, "hj_set_option: denoise sigmas are in 1/1000, 1..1000000");
+        if (!strcmp(key + 14, "color_milli")) c->opt_denoise_sigma_color_milli = (int)value;
+        else if (!strcmp(key + 14, "normal_milli")) c->opt_denoise_sigma_normal_milli = (int)value;
+        else if (!strcmp(key + 14, "albedo_milli")) c->opt_denoise_sigma_albedo_milli = (int)value;
+        else { c->err = std::string("hj_set_option: unknown option '") + key + "'"; return HJ_ERR_INVALID; }
+    }
     else { c->err = std::string("hj_set_option: unknown option '") + key + "'"; return HJ_ERR_INVALID; }
     return HJ_OK;
 }
@@ -109,7 +120,7 @@ int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
     for (uint32_t i = 0; i < d->n_light_prims; i++)
         HJ_REQUIRE(c, d->light_prim_ids && d->light_prim_emission && d->light_prim_ids[i] < d->n_triangles, HJ_ERR_INVALID, "hj_scene_upload: bad light primitive list");
     HJ_CUDA(c, cudaSetDevice(c->device));
-    c->have_scene = c->have_accel = c->have_frame = false;
+    c->have_scene = c->have_accel = c->have_frame = c->have_output = false;
     c->bvh.have_topology = false;
     int rc;
     const size_t nv = d->n_vertices, nt = d->n_triangles;
@@ -256,6 +267,8 @@ static int aov_info(hj_ctx* c, int aov, void** p, size_t* bytes) {
         case HJ_AOV_ACCUM: *p = c->aov_accum.p; *bytes = wh * 16; return HJ_OK;
         case HJ_AOV_PATH_RADIANCE: *p = c->fp.debug_paths ? c->aov_path_rad.p : nullptr; *bytes = ns * wh * 16; return HJ_OK;
         case HJ_AOV_PATH_IDS: *p = c->fp.debug_paths ? c->aov_path_ids.p : nullptr; *bytes = ns * wh * 8; return HJ_OK;
+        case HJ_AOV_OUTPUT: *p = c->have_output ? c->aov_output.p : nullptr; *bytes = (size_t)c->out_w * c->out_h * 16; return HJ_OK;
+        case HJ_AOV_OUTPUT_RGBA8: *p = c->have_output ? c->aov_output_rgba8.p : nullptr; *bytes = (size_t)c->out_w * c->out_h * 4; return HJ_OK;
     }
     return HJ_ERR_INVALID;
 }
@@ -265,12 +278,21 @@ int hj_readback(hj_ctx* c, int aov, void* dst, size_t bytes) {
     HJ_REQUIRE(c, c->have_frame, HJ_ERR_NO_FRAME, "hj_readback: nothing rendered yet");
     void* p = nullptr; size_t want = 0;
     HJ_REQUIRE(c, aov_info(c, aov, &p, &want) == HJ_OK, HJ_ERR_INVALID, "hj_readback: unknown AOV");
-    HJ_REQUIRE(c, p != nullptr, HJ_ERR_INVALID, "hj_readback: AOV not recorded (debug_paths was 0)");
+    HJ_REQUIRE(c, p != nullptr, HJ_ERR_INVALID, "hj_readback: AOV not recorded (debug_paths was 0 / hj_post not called for this frame)");
     HJ_REQUIRE(c, bytes == want, HJ_ERR_INVALID, "hj_readback: size mismatch");
     HJ_CUDA(c, cudaSetDevice(c->device));
     HJ_CUDA(c, cudaMemcpyAsync(dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
     HJ_CUDA(c, cudaStreamSynchronize(c->stream));
     return HJ_OK;
+}
+
+int hj_post(hj_ctx* c, int mode) {
+    if (!c) return HJ_ERR_INVALID;
+    HJ_REQUIRE(c, c->have_frame, HJ_ERR_NO_FRAME, "hj_post: nothing rendered yet");
+    HJ_REQUIRE(c, mode >= HJ_POST_PASSTHROUGH && mode <= HJ_POST_DENOISE_UPSCALE2X, HJ_ERR_INVALID, "hj_post: unknown mode");
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    if (!c->ev_post0) { HJ_CUDA(c, cudaEventCreate(&c->ev_post0)); HJ_CUDA(c, cudaEventCreate(&c->ev_post1)); }
+    return hj_post_run(c, mode);
 }
 
 int hj_host_pin(hj_ctx* c, void* ptr, size_t bytes) {

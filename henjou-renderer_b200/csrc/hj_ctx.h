@@ -80,6 +80,11 @@ struct hj_ctx {
     hj_frame_params fp{};
     DevBuf aov_color, aov_albedo, aov_normal, aov_rgba8, aov_accum, aov_path_rad, aov_path_ids;
     uint32_t fb_w = 0, fb_h = 0;
+    // post stage (hj_post.cu): output plane of the last hj_post, a-trous ping-pong planes
+    DevBuf aov_output, aov_output_rgba8, post_tmp[2];
+    uint32_t out_w = 0, out_h = 0; bool have_output = false;
+    cudaEvent_t ev_post0 = nullptr, ev_post1 = nullptr;
+    int opt_denoise_iterations = 5, opt_denoise_sigma_color_milli = 2000, opt_denoise_sigma_normal_milli = 100, opt_denoise_sigma_albedo_milli = 50;   // r01-v sweep, tools/post_bench.py
     hj_stats stats{};
     // option "time_stages": event pairs around every traversal (kind 0) and shading (kind 1) launch of the last frame
     std::vector<cudaEvent_t> ev_pool; std::vector<int> ev_kind;
@@ -104,5 +109,7 @@ int hj_bvh_build(hj_ctx* c, int mode);
 // hj_wavefront.cu
 int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp);
 int hj_wavefront_finalize(hj_ctx* c);
+// hj_post.cu
+int hj_post_run(hj_ctx* c, int mode);
 int hj_wavefront_stats(hj_ctx* c);
 int hj_trace_batch(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, uint32_t* prim_host, float* tuv_host);

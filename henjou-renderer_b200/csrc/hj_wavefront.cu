@@ -671,7 +671,7 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     launches++;
     HJ_CUDA(c, cudaEventRecord(c->ev1, st));
     HJ_CUDA(c, cudaGetLastError());
-    c->fp = *fp; c->have_frame = true;
+    c->fp = *fp; c->have_frame = true; c->have_output = false;
     c->stats.kernel_launches = launches;
     c->stats.paths = (uint64_t)ns * WH;
     c->stats.passes = n_passes;

@@ -1,8 +1,8 @@
 // henjou_b200_cli — headless host of the B200 path tracer: reads the reference's render_option.json (+ ./fps.txt) and its
 // glTF scene, runs the reference's frame loop (Renderer::initializeAndRender, /root/reference/include/renderer/
 // renderer.h:1053-1318) over the C ABI of libhenjou_b200.so instead of OptiX, and writes `<image_name>_<NNN>.png` into
-// the working directory (renderer.h:1285-1302). No window, no GL, no denoiser (Render_mode "Default" is a pass-through
-// in the reference; the Denoise modes fall back to it with a warning).
+// the working directory (renderer.h:1285-1302). No window, no GL. The denoise step (renderer.h:1256-1283) is hj_post:
+// Render_mode "Default" is a pass-through as in the reference; the Denoise modes run the a-trous stand-in for the OptiX network.
 //
 //   henjou_b200_cli [render_option.json] [--device N] [--spp N] [--frames BEGIN END] [--width W --height H]
 //                   [--out-dir DIR] [--dump-scene FILE] [--rebuild] [--quiet]
@@ -142,8 +142,8 @@ int main(int argc, char** argv) {
         if (w_override > 0) opt.image_width = w_override;
         if (h_override > 0) opt.image_height = h_override;
         LOGI("image %dx%d, %u spp, frames [%d,%d) at %u fps, mode %s", opt.image_width, opt.image_height, opt.max_spp, opt.start_frame, opt.end_frame, opt.fps, opt.render_mode.c_str());
-        if (opt.render_mode != "Default" && opt.render_mode != "Debug")
-            LOGI("Render_mode %s needs the OptiX AI denoiser (unavailable on this box): rendering as Default", opt.render_mode.c_str());
+        if (opt.render_mode != "Default")
+            LOGI("Render_mode %s: the OptiX AI denoiser is unavailable on this box; hj_post's a-trous filter (albedo + normal guided) stands in", opt.render_mode.c_str());
         load_gltf(join(base, opt.gltf_path), opt.gltf_name, opt, sc);
         // setSky (renderer.h:802-811): the HDR image, or the constant default when use_IBL is off / the file is missing
         sc.ibl = {opt.scene_sky_default[0], opt.scene_sky_default[1], opt.scene_sky_default[2], 0.0f}; sc.ibl_w = sc.ibl_h = 1;
@@ -181,7 +181,14 @@ int main(int argc, char** argv) {
     HJ_CHECK(ctx, hj_scene_upload(ctx, &d));
 
     const double t_start = now_s();
-    std::vector<uint8_t> rgba((size_t)opt.image_width * opt.image_height * 4);
+    // renderer.h:1089-1115: UpScale2X renders at half the resolution; Default passes the colour AOV through (blendFactor 1);
+    // every other mode (Denoise, Debug) runs the HDR denoiser
+    const bool upscale = opt.render_mode == "DenoiseUpScale2X";
+    const int post_mode = upscale ? HJ_POST_DENOISE_UPSCALE2X : (opt.render_mode == "Default" ? HJ_POST_PASSTHROUGH : HJ_POST_DENOISE);
+    const uint32_t in_w = upscale ? (uint32_t)opt.image_width / 2u : (uint32_t)opt.image_width, in_h = upscale ? (uint32_t)opt.image_height / 2u : (uint32_t)opt.image_height;
+    const uint32_t out_w = upscale ? 2u * in_w : in_w, out_h = upscale ? 2u * in_h : in_h;
+    if (in_w == 0 || in_h == 0) { fprintf(stderr, "henjou_b200_cli: image too small for Render_mode %s\n", opt.render_mode.c_str()); hj_destroy(ctx); return 1; }
+    std::vector<uint8_t> rgba((size_t)out_w * out_h * 4);
     bool first = true;
     for (int frame = opt.start_frame; frame < opt.end_frame; frame++) {          // renderer.h:1126
         const float time = frame / float(opt.fps);                                // :1128
@@ -189,20 +196,21 @@ int main(int argc, char** argv) {
         instance_matrices(sc, time, xf, inv);                                     // updateIASMatrix, :1133
         HJ_CHECK(ctx, hj_accel_build(ctx, xf.data(), inv.data(), sc.n_instances(), (first || rebuild) ? HJ_ACCEL_BUILD : HJ_ACCEL_REFIT));
         hj_frame_params fp{};
-        fp.width = (uint32_t)opt.image_width; fp.height = (uint32_t)opt.image_height;
+        fp.width = in_w; fp.height = in_h;
         fp.spp = opt.max_spp; fp.sample_begin = 0; fp.sample_end = opt.max_spp; fp.frame = (uint32_t)frame;      // :1186-1187
         camera_basis(opt, sc, time, fp);
         fp.ibl_intensity = opt.IBL_intensity;
         fp.integrator = opt.integrator; fp.max_depth = opt.max_depth; fp.tonemap = opt.tonemap; fp.pixel_jitter = 1;
         HJ_CHECK(ctx, hj_render(ctx, &fp));                                       // optixLaunch + sync, :1241-1242
-        HJ_CHECK(ctx, hj_readback(ctx, HJ_AOV_RGBA8, rgba.data(), rgba.size())); // float4ConvertColor, :1281
+        HJ_CHECK(ctx, hj_post(ctx, post_mode));                                   // denosier_manager.denoise(), :1262-1271
+        HJ_CHECK(ctx, hj_readback(ctx, HJ_AOV_OUTPUT_RGBA8, rgba.data(), rgba.size()));   // float4ConvertColor(AOV_Output), :1281
         char num[16]; snprintf(num, sizeof num, "%03d", frame);                   // :1291-1301
         const std::string name = out_dir + opt.image_name + "_" + num + ".png";
-        try { png_write(name, rgba.data(), opt.image_width, opt.image_height, true); }
+        try { png_write(name, rgba.data(), (int)out_w, (int)out_h, true); }
         catch (const std::exception& e) { fprintf(stderr, "henjou_b200_cli: %s\n", e.what()); hj_destroy(ctx); return 1; }
         hj_stats st{}; hj_get_stats(ctx, &st);
         const double el = now_s() - t_start;
-        LOGI("frame %d: accel %.2f ms, render %.2f ms, %.1f Mrays/s -> %s   (time limit: %.1f s / %.1f s)", frame, st.ms_accel, st.ms_render,
+        LOGI("frame %d: accel %.2f ms, render %.2f ms, post %.2f ms, %.1f Mrays/s -> %s   (time limit: %.1f s / %.1f s)", frame, st.ms_accel, st.ms_render, st.ms_post,
              (st.rays_extend + st.rays_shadow) / (st.ms_render * 1e3), name.c_str(), el, opt.time_limit * 60.0f);
         first = false;
     }

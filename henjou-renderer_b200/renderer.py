@@ -46,6 +46,7 @@ def load_library():
     L.hj_finalize.argtypes = [vp]
     L.hj_get_stats.argtypes = [vp, C.POINTER(abi.hj_stats)]
     L.hj_trace.argtypes = [vp, abi.f32p, C.c_uint64, C.c_int, abi.u32p, abi.f32p]
+    L.hj_post.argtypes = [vp, C.c_int]
     L.hj_host_pin.argtypes = [vp, vp, C.c_size_t]
     L.hj_host_unpin.argtypes = [vp, vp]
     L.hj_comm_unique_id.argtypes = [vp]
@@ -96,10 +97,17 @@ class Renderer:
     def sync(self):
         self._check(self.L.hj_sync(self.ctx), "hj_sync")
 
+    def post(self, mode=abi.POST_PASSTHROUGH):
+        """OptixDenoiserManager::denoise + float4ConvertColor (renderer.h:1256-1283) -> AOV_OUTPUT / AOV_OUTPUT_RGBA8."""
+        self._check(self.L.hj_post(self.ctx, int(mode)), "hj_post")
+        self.post_scale = 2 if mode == abi.POST_DENOISE_UPSCALE2X else 1
+
     def readback(self, aov, out=None):
         W, H = self.fp.width, self.fp.height
+        if aov in (abi.AOV_OUTPUT, abi.AOV_OUTPUT_RGBA8):
+            W, H = W * getattr(self, "post_scale", 1), H * getattr(self, "post_scale", 1)
         ns = self.fp.sample_end - self.fp.sample_begin
-        shape, dt = {abi.AOV_RGBA8: ((H, W, 4), np.uint8), abi.AOV_PATH_RADIANCE: ((ns, H, W, 4), np.float32),
+        shape, dt = {abi.AOV_RGBA8: ((H, W, 4), np.uint8), abi.AOV_OUTPUT_RGBA8: ((H, W, 4), np.uint8), abi.AOV_PATH_RADIANCE: ((ns, H, W, 4), np.float32),
                      abi.AOV_PATH_IDS: ((ns, H, W, 2), np.uint32)}.get(aov, ((H, W, 4), np.float32))
         if out is None:
             out = np.empty(shape, dt)

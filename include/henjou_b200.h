@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define HJ_ABI_VERSION 1
+#define HJ_ABI_VERSION 2
 
 typedef struct hj_ctx hj_ctx;
 
@@ -54,6 +54,8 @@ typedef enum hj_aov {
     HJ_AOV_RGBA8 = 3,        /* uchar4[W*H]  Params::image; float4ConvertColor semantics (renderer.h:87)   */
     HJ_AOV_ACCUM = 4,        /* float4[W*H]  raw radiance SUM of this context's sample slice (multi-GPU)   */
     HJ_AOV_PATH_RADIANCE = 5,/* float4[n_samples*W*H] debug: per-sample radiance rgb, w = #rays of path     */
+    HJ_AOV_OUTPUT = 7,       /* float4[OW*OH] result of hj_post: AOV_Output (renderer.h:1106), OW x OH = W x H or 2W x 2H */
+    HJ_AOV_OUTPUT_RGBA8 = 8, /* uchar4[OW*OH] float4ConvertColor of HJ_AOV_OUTPUT: the pixels of the written PNG     */
     HJ_AOV_PATH_IDS = 6      /* uint32[2*n_samples*W*H] debug: {first-hit global prim id | 0xffffffff,
                                                                hash of every closest-hit id on the path}   */
 } hj_aov;
@@ -150,6 +152,8 @@ typedef struct hj_stats {
     uint32_t bvh_depth;           /* levels of the 8-wide tree                                                  */
     uint32_t max_nodes_per_ray;   /* worst single ray of the last hj_render (only with "count_fetches")         */
     uint32_t max_tris_per_ray;
+    float ms_post;                /* device time of the last hj_post                                            */
+    uint32_t post_launches;       /* kernels launched by the last hj_post                                       */
     uint32_t passes;              /* wavefront passes of the last hj_render (each: max_depth x (1 extend + 1 shadow + 1 MIS) traversal launches) */
 } hj_stats;
 
@@ -181,6 +185,18 @@ int hj_sync(hj_ctx* ctx);
 
 /* Copies an AOV of the last rendered frame into caller memory; `bytes` must be the exact size. */
 int hj_readback(hj_ctx* ctx, int aov, void* dst, size_t bytes);
+
+/* The stage between the colour AOV and the written image — OptixDenoiserManager::denoise() (denoiser.h:143-177) as
+ * driven per frame by renderer.h:1256-1283, plus float4ConvertColor (renderer.h:87-101). Reads the COLOR / ALBEDO /
+ * NORMAL AOVs of the last frame, writes HJ_AOV_OUTPUT and HJ_AOV_OUTPUT_RGBA8.
+ *   HJ_POST_PASSTHROUGH        Render_mode "Default" (blendFactor 1, renderer.h:1113-1115): output == colour AOV, exact
+ *   HJ_POST_DENOISE            Render_mode "Denoise" / "Debug" (HDR model): edge-avoiding a-trous filter guided by albedo +
+ *                              normal — the stand-in for the OptiX AI network, which has no source (parity unpinned)
+ *   HJ_POST_DENOISE_UPSCALE2X  Render_mode "DenoiseUpScale2X" (renderer.h:1096-1099: the frame is rendered at W/2 x H/2):
+ *                              the same filter, then a 2x enlargement; output is 2W x 2H of the rendered frame
+ * Options (hj_set_option): "denoise_iterations" (0..8, default 5), "denoise_sigma_{color,normal,albedo}_milli" (1/1000; defaults 2000, 100, 50). */
+typedef enum hj_post_mode { HJ_POST_PASSTHROUGH = 0, HJ_POST_DENOISE = 1, HJ_POST_DENOISE_UPSCALE2X = 2 } hj_post_mode;
+int hj_post(hj_ctx* ctx, int mode);
 
 /* Page-locks / releases caller memory (cudaHostRegister) so that hj_scene_upload / hj_readback DMA straight from / into it
  * instead of going through the driver's staging copies; for hosts without the CUDA headers. The reference keeps its

@@ -26,13 +26,13 @@ def test_exports_match_header(lib):
     assert declared == set(abi.EXPORTS), declared ^ set(abi.EXPORTS)
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.hj_abi_version() == 1
+    assert lib.hj_abi_version() == 2
 
 
 def test_struct_sizes():
     assert C.sizeof(abi.hj_material) == 25 * 4
     assert C.sizeof(abi.hj_frame_params) == 6 * 4 + 12 * 4 + 2 * 4 + 6 * 4
-    assert C.sizeof(abi.hj_stats) == 6 * 8 + 4 * 4 + 6 * 4
+    assert C.sizeof(abi.hj_stats) == 6 * 8 + 4 * 4 + 8 * 4
 
 
 def test_no_cpu_fallback(lib):

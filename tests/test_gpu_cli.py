@@ -66,3 +66,29 @@ def test_cli_without_gpu_library_fails_loudly(tmp_path):
     r = subprocess.run([CLI, "render_option.json"], cwd=str(tmp_path), capture_output=True, text=True, timeout=60)
     assert r.returncode != 0 and "cannot open" in r.stderr
     assert not list(tmp_path.glob("*.png"))
+
+
+def test_cli_render_modes(tmp_path):
+    """Render_mode (render_json_loader.h:115-136, renderer.h:1089-1115): Denoise = hj_post on the same frame;
+    DenoiseUpScale2X renders at half the resolution and writes the full-size image."""
+    scene = hj.load_npz(os.path.join(ROOT, "tests", "golden", "cornelbox.npz"))
+    scene.set_sky((0.8, 0.8, 0.8))
+    W, H, spp = 96, 64, 4
+    npz_to_gltf.export_gltf(scene, str(tmp_path / "Model"), "c")
+    r = hj.Renderer(0)
+    r.upload(scene)
+    xf, inv = scene.transforms(float(np.float32(1) / np.float32(24)))
+    for mode, post, (w, h) in (("Denoise", abi.POST_DENOISE, (W, H)), ("DenoiseUpScale2X", abi.POST_DENOISE_UPSCALE2X, (W // 2, H // 2))):
+        npz_to_gltf.write_render_option(str(tmp_path / "render_option.json"), "./Model/", "c.gltf", mode, W, H, spp, fps=24, start_frame=1,
+                                        end_frame=2, render_mode=mode)
+        p = subprocess.run([CLI, "render_option.json"], cwd=str(tmp_path), capture_output=True, text=True, timeout=300)
+        assert p.returncode == 0, p.stderr
+        got = npz_to_gltf.read_png(str(tmp_path / (mode + "_001.png")))
+        assert got.shape == (H, W, 4)
+        r.build_accel(xf, inv)
+        r.render(hj.frame_params(scene, w, h, spp, frame=1, fps=24, camera=scene.camera))
+        r.post(post)
+        want = r.readback(abi.AOV_OUTPUT_RGBA8)[::-1]
+        diff = np.abs(got.astype(np.int32) - want.astype(np.int32))
+        assert (diff > 1).any(-1).mean() < 2e-2 and diff.mean() < 0.05, (mode, (diff > 1).any(-1).mean(), diff.mean())
+    r.close()

@@ -190,10 +190,10 @@ def export_gltf(scene, out_dir, name, fov_fallback=None):
 
 def write_render_option(path, gltf_dir, gltf_name, image_name, width, height, spp, sky=(0.8, 0.8, 0.8), fps=24, start_frame=1,
                         end_frame=2, camera_position=(0, 1, -7), camera_direction=(0, 0, 1), camera_fov=45.0, lut_path="./LUT/Thin_Film_LUT.png",
-                        allow_camera_animation=True, integrator=None):
+                        allow_camera_animation=True, integrator=None, render_mode="Default"):
     """A render_option.json with the reference's schema (HenjouRenderer/render_option.json)."""
     j = dict(Image=dict(image_width=width, image_height=height, image_name=image_name, image_directory="./", max_spp=spp),
-             Render_mode="Default", GLTF_file=dict(gltf_filepath=gltf_dir, gltf_filename=gltf_name),
+             Render_mode=render_mode, GLTF_file=dict(gltf_filepath=gltf_dir, gltf_filename=gltf_name),
              Camera=dict(allow_camera_animation=allow_camera_animation, camera_position=list(camera_position),
                          camera_direction=list(camera_direction), camera_fov=camera_fov),
              PTX_File=dict(ptxfile_path="../lib/ptx/Release/HenjouRenderer_generated_henjouRendererCU.cu.optixir"),
