@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <future>
 #include <string>
 #include <vector>
 #include "hj_gltf.h"
@@ -115,7 +116,7 @@ static double now_s() { return std::chrono::duration<double>(std::chrono::steady
 int main(int argc, char** argv) {
     std::string option_path = "./render_option.json", out_dir = "./", dump_path;
     int device = 0, spp_override = -1, f_begin = -1, f_end = -1, w_override = -1, h_override = -1;
-    bool rebuild = false;
+    bool rebuild = false, enforce_limit = false;
     for (int i = 1; i < argc; i++) {
         const std::string a = argv[i];
         auto need = [&](int n) { if (i + n >= argc) { fprintf(stderr, "henjou_b200_cli: %s needs %d argument(s)\n", a.c_str(), n); exit(1); } };
@@ -127,8 +128,9 @@ int main(int argc, char** argv) {
         else if (a == "--out-dir") { need(1); out_dir = argv[++i]; if (out_dir.back() != '/') out_dir += '/'; }
         else if (a == "--dump-scene") { need(1); dump_path = argv[++i]; }
         else if (a == "--rebuild") rebuild = true;
+        else if (a == "--enforce-time-limit") enforce_limit = true;
         else if (a == "--quiet") g_quiet = true;
-        else if (a == "--help" || a == "-h") { printf("usage: henjou_b200_cli [render_option.json] [--device N] [--spp N] [--frames BEGIN END] [--width W --height H] [--out-dir DIR] [--dump-scene FILE] [--rebuild] [--quiet]\n"); return 0; }
+        else if (a == "--help" || a == "-h") { printf("usage: henjou_b200_cli [render_option.json] [--device N] [--spp N] [--frames BEGIN END] [--width W --height H] [--out-dir DIR] [--dump-scene FILE] [--rebuild] [--enforce-time-limit] [--quiet]\n"); return 0; }
         else if (a[0] != '-') option_path = a;
         else { fprintf(stderr, "henjou_b200_cli: unknown option %s\n", a.c_str()); return 1; }
     }
@@ -188,7 +190,16 @@ int main(int argc, char** argv) {
     const uint32_t in_w = upscale ? (uint32_t)opt.image_width / 2u : (uint32_t)opt.image_width, in_h = upscale ? (uint32_t)opt.image_height / 2u : (uint32_t)opt.image_height;
     const uint32_t out_w = upscale ? 2u * in_w : in_w, out_h = upscale ? 2u * in_h : in_h;
     if (in_w == 0 || in_h == 0) { fprintf(stderr, "henjou_b200_cli: image too small for Render_mode %s\n", opt.render_mode.c_str()); hj_destroy(ctx); return 1; }
-    std::vector<uint8_t> rgba((size_t)out_w * out_h * 4);
+    // the PNG of frame N is deflated and written by a worker while the GPU renders frame N+1 (two image buffers in turn)
+    std::vector<uint8_t> rgba_buf[2] = {std::vector<uint8_t>((size_t)out_w * out_h * 4), std::vector<uint8_t>((size_t)out_w * out_h * 4)};
+    std::future<std::string> writer;
+    auto join_writer = [&]() -> bool {
+        if (!writer.valid()) return true;
+        const std::string err = writer.get();
+        if (!err.empty()) fprintf(stderr, "henjou_b200_cli: %s\n", err.c_str());
+        return err.empty();
+    };
+    int n_done = 0;
     bool first = true;
     for (int frame = opt.start_frame; frame < opt.end_frame; frame++) {          // renderer.h:1126
         const float time = frame / float(opt.fps);                                // :1128
@@ -203,17 +214,25 @@ int main(int argc, char** argv) {
         fp.integrator = opt.integrator; fp.max_depth = opt.max_depth; fp.tonemap = opt.tonemap; fp.pixel_jitter = 1;
         HJ_CHECK(ctx, hj_render(ctx, &fp));                                       // optixLaunch + sync, :1241-1242
         HJ_CHECK(ctx, hj_post(ctx, post_mode));                                   // denosier_manager.denoise(), :1262-1271
+        std::vector<uint8_t>& rgba = rgba_buf[n_done & 1];                        // its previous user (frame N-2) was joined below
         HJ_CHECK(ctx, hj_readback(ctx, HJ_AOV_OUTPUT_RGBA8, rgba.data(), rgba.size()));   // float4ConvertColor(AOV_Output), :1281
         char num[16]; snprintf(num, sizeof num, "%03d", frame);                   // :1291-1301
         const std::string name = out_dir + opt.image_name + "_" + num + ".png";
-        try { png_write(name, rgba.data(), (int)out_w, (int)out_h, true); }
-        catch (const std::exception& e) { fprintf(stderr, "henjou_b200_cli: %s\n", e.what()); hj_destroy(ctx); return 1; }
+        if (!join_writer()) { hj_destroy(ctx); return 1; }
+        writer = std::async(std::launch::async, [name, &rgba, out_w, out_h]() -> std::string {
+            try { png_write(name, rgba.data(), (int)out_w, (int)out_h, true); } catch (const std::exception& e) { return e.what(); }
+            return std::string();
+        });
+        n_done++;
         hj_stats st{}; hj_get_stats(ctx, &st);
         const double el = now_s() - t_start;
         LOGI("frame %d: accel %.2f ms, render %.2f ms, post %.2f ms, %.1f Mrays/s -> %s   (time limit: %.1f s / %.1f s)", frame, st.ms_accel, st.ms_render, st.ms_post,
              (st.rays_extend + st.rays_shadow) / (st.ms_render * 1e3), name.c_str(), el, opt.time_limit * 60.0f);
         first = false;
+        // the check the reference carries commented out (renderer.h:1247-1254): stop once the sequence is over its budget
+        if (enforce_limit && el > opt.time_limit * 60.0f) { LOGI("Over Time Limit: %d of %d frames written", n_done, opt.end_frame - opt.start_frame); break; }
     }
+    const bool ok = join_writer();
     hj_destroy(ctx);
-    return 0;
+    return ok ? 0 : 1;
 }

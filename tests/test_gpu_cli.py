@@ -92,3 +92,21 @@ def test_cli_render_modes(tmp_path):
         diff = np.abs(got.astype(np.int32) - want.astype(np.int32))
         assert (diff > 1).any(-1).mean() < 2e-2 and diff.mean() < 0.05, (mode, (diff > 1).any(-1).mean(), diff.mean())
     r.close()
+
+
+def test_cli_time_limit_and_frame_sequence(tmp_path):
+    """Frames are written by a worker while the next one renders: every PNG of the sequence must be there and differ
+    (animated camera); --enforce-time-limit applies the check the reference carries commented out (renderer.h:1247-1254)."""
+    scene = hj.load_npz(os.path.join(ROOT, "tests", "golden", "cornelbox.npz"))
+    npz_to_gltf.export_gltf(scene, str(tmp_path / "Model"), "c")
+    npz_to_gltf.write_render_option(str(tmp_path / "render_option.json"), "./Model/", "c.gltf", "seq", 64, 48, 2, fps=24, start_frame=1, end_frame=6)
+    p = subprocess.run([CLI, "render_option.json"], cwd=str(tmp_path), capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr
+    imgs = [npz_to_gltf.read_png(str(tmp_path / ("seq_%03d.png" % f))) for f in range(1, 6)]
+    assert all(im.shape == (48, 64, 4) for im in imgs)
+    assert all((imgs[i] != imgs[i + 1]).any() for i in range(4))          # frame index = RNG scramble: no two frames alike
+    npz_to_gltf.write_render_option(str(tmp_path / "render_option.json"), "./Model/", "c.gltf", "lim", 64, 48, 2, fps=24, start_frame=1, end_frame=6,
+                                    time_limit=0.0)
+    p = subprocess.run([CLI, "render_option.json", "--enforce-time-limit"], cwd=str(tmp_path), capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0 and "Over Time Limit" in p.stdout + p.stderr
+    assert sorted(f.name for f in tmp_path.glob("lim_*.png")) == ["lim_001.png"]
