@@ -242,7 +242,8 @@ def gpu_arm(args, rank, world, local_rank):
         tsum = tt.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         e_t, e_rays = float(tmax[0]), int(tsum[1])
     out["e2e"] = dict(value=round(e_rays / e_t / 1e6, 2), unit="Mrays/s", h2d_bytes_per_step=int(h2d) * world, d2h_bytes_per_step=int(d2h) * world,
-                      ms_per_step=round(1e3 * e_t / args.steps, 3), checksum=float(color[..., :3].mean()),
+                      ms_per_step=round(1e3 * e_t / args.steps, 3), checksum=float(np.nanmean(np.where(np.isfinite(color[..., :3]), color[..., :3], np.nan))),
+                      non_finite_pixels=int((~np.isfinite(color[..., :3]).all(-1)).sum()),
                       host_memory="pageable" if args.pageable else "pinned (hj_host_pin)")
     r.unpin(*pinned)
     if rank == 0 and world == 1:
