@@ -198,6 +198,12 @@ __global__ void k_karras(const uint64_t* __restrict__ keys, int n, uint32_t* lef
     if (i == 0) parent[0] = 0xffffffffu;
 }
 
+// 1.0f when the triangle's material emits (the test finish_mis applies to a hit, hj_wavefront.cu): carried in the .w of the
+// binary boxes (max over children) so that the collapse can mark the wide-node children that contain emitters
+HJ_DI float tri_emits(const DevScene& S, uint32_t prim) {
+    return S.materials[__float_as_uint(S.tri_attr[4 * (size_t)prim + 3].w)].is_light ? 1.0f : 0.0f;
+}
+
 __global__ void k_fit(const DevScene S, const uint32_t* __restrict__ sorted, int n, const uint32_t* __restrict__ left, const uint32_t* __restrict__ right,
                       const uint32_t* __restrict__ parent, uint32_t* flags, float4* blo, float4* bhi) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -207,7 +213,8 @@ __global__ void k_fit(const DevScene S, const uint32_t* __restrict__ sorted, int
     float3 lo = f3(fminf(a.x, fminf(b.x, c.x)), fminf(a.y, fminf(b.y, c.y)), fminf(a.z, fminf(b.z, c.z)));
     float3 hi = f3(fmaxf(a.x, fmaxf(b.x, c.x)), fmaxf(a.y, fmaxf(b.y, c.y)), fmaxf(a.z, fmaxf(b.z, c.z)));
     uint32_t id = (uint32_t)(n - 1 + j);
-    blo[id] = f4(lo, 0.0f); bhi[id] = f4(hi, 0.0f);
+    float em = tri_emits(S, sorted[j]);
+    blo[id] = f4(lo, em); bhi[id] = f4(hi, 0.0f);
     if (n == 1) return;
     uint32_t p = parent[id];
     while (p != 0xffffffffu) {
@@ -217,7 +224,8 @@ __global__ void k_fit(const DevScene S, const uint32_t* __restrict__ sorted, int
         const float4 ll = __ldcg(blo + l), lh = __ldcg(bhi + l), rl = __ldcg(blo + r), rh = __ldcg(bhi + r);   // L2 loads: written by other SMs
         lo = f3(fminf(ll.x, rl.x), fminf(ll.y, rl.y), fminf(ll.z, rl.z));
         hi = f3(fmaxf(lh.x, rh.x), fmaxf(lh.y, rh.y), fmaxf(lh.z, rh.z));
-        blo[p] = f4(lo, 0.0f); bhi[p] = f4(hi, 0.0f);
+        em = fmaxf(ll.w, rl.w);
+        blo[p] = f4(lo, em); bhi[p] = f4(hi, 0.0f);
         p = parent[p];
     }
 }
@@ -237,7 +245,7 @@ __global__ void k_ploc_init(const DevScene S, const uint32_t* __restrict__ sorte
     if (j >= n) return;
     const float4* P = S.tri_pos + 3 * (size_t)sorted[j];
     const float3 a = f3(P[0]), b = f3(P[1]), c = f3(P[2]);
-    const float4 lo = make_float4(fminf(a.x, fminf(b.x, c.x)), fminf(a.y, fminf(b.y, c.y)), fminf(a.z, fminf(b.z, c.z)), 0.0f);
+    const float4 lo = make_float4(fminf(a.x, fminf(b.x, c.x)), fminf(a.y, fminf(b.y, c.y)), fminf(a.z, fminf(b.z, c.z)), tri_emits(S, sorted[j]));
     const float4 hi = make_float4(fmaxf(a.x, fmaxf(b.x, c.x)), fmaxf(a.y, fmaxf(b.y, c.y)), fmaxf(a.z, fmaxf(b.z, c.z)), 0.0f);
     const uint32_t id = (uint32_t)(n - 1 + j);
     cid[j] = id; clo[j] = lo; chi[j] = hi; blo[id] = lo; bhi[id] = hi;
@@ -284,7 +292,7 @@ __global__ void __launch_bounds__(PLOC_THREADS) k_ploc_merge(int n, int n_leaves
                 const uint32_t id = atomicAdd(node_ctr, 1u);
                 const uint32_t a = cid[i], b = cid[j];
                 const float4 alo = clo[i], ahi = chi[i], xlo = clo[j], xhi = chi[j];
-                const float4 lo = make_float4(fminf(alo.x, xlo.x), fminf(alo.y, xlo.y), fminf(alo.z, xlo.z), 0.0f);
+                const float4 lo = make_float4(fminf(alo.x, xlo.x), fminf(alo.y, xlo.y), fminf(alo.z, xlo.z), fmaxf(alo.w, xlo.w));
                 const float4 hi = make_float4(fmaxf(ahi.x, xhi.x), fmaxf(ahi.y, xhi.y), fmaxf(ahi.z, xhi.z), 0.0f);
                 left[id] = a; right[id] = b; parent[a] = id; parent[b] = id;
                 cnt[id] = (a >= (uint32_t)(n_leaves - 1) ? 1u : cnt[a]) + (b >= (uint32_t)(n_leaves - 1) ? 1u : cnt[b]);
@@ -405,7 +413,7 @@ __global__ void k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32
         while (e < 254u && lo[ax] + 255.0f * __uint_as_float(e << 23) < hi[ax]) e++;
         eb[ax] = e; scale[ax] = __uint_as_float(e << 23);
     }
-    uint32_t imask = 0, n_int = 0, n_tri = 0;
+    uint32_t imask = 0, n_int = 0, n_tri = 0, em_word = 0;
     uint32_t meta[8], qlo[3][8], qhi[3][8];
     for (int s = 0; s < 8; s++) {
         meta[s] = 0;
@@ -414,8 +422,18 @@ __global__ void k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32
         if (k < 0) continue;
         const uint32_t id = ch[k];
         const uint32_t cnt = bn_count(a, id);
-        if (id < (uint32_t)(a.n - 1) && cnt > a.leaf_max) { imask |= 1u << s; n_int++; meta[s] = (1u << 5) | (24u + (uint32_t)s); }
-        else { meta[s] = (((1u << cnt) - 1u) << 5) | n_tri; n_tri += cnt; }
+        if (id < (uint32_t)(a.n - 1) && cnt > a.leaf_max) {
+            imask |= 1u << s; n_int++; meta[s] = (1u << 5) | (24u + (uint32_t)s);
+            if (a.blo[id].w > 0.0f) em_word |= 1u << (24 + s);
+        } else {
+            meta[s] = (((1u << cnt) - 1u) << 5) | n_tri;
+            if (a.blo[id].w > 0.0f) {                     // which of its (<= 3) triangles emit
+                uint32_t lv[4];
+                const uint32_t m = (uint32_t)bn_leaves(a, id, lv);
+                for (uint32_t j = 0; j < m; j++) if (a.blo[(uint32_t)(a.n - 1) + lv[j]].w > 0.0f) em_word |= 1u << (n_tri + j);
+            }
+            n_tri += cnt;
+        }
         for (int ax = 0; ax < 3; ax++) {
             int ql = (int)floorf((clo[k][ax] - lo[ax]) / scale[ax]);
             ql = max(0, min(255, ql));
@@ -441,7 +459,7 @@ __global__ void k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32
     N[3] = make_uint4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
     N[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
     N[5] = make_uint4(cm[2], cm[3], cm[4], cm[5]);
-    N[6] = make_uint4(cm[6], cm[7], pack4(meta), pack4(meta + 4));
+    N[6] = make_uint4(cm[6], cm[7], em_word, 0u);
     // children: queue the internal ones (contiguous, in slot order), copy the triangles of the leaves
     const uint32_t qbase = n_int ? atomicAdd(&a.counters[2], n_int) : 0u;
     uint32_t r = 0;

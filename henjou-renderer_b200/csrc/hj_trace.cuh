@@ -6,13 +6,14 @@
 //   q0: origin.xyz (float bits) | ex | ey<<8 | ez<<16 | imask<<24      (e* = biased float exponents of the grid step)
 //   q1: child_base (first internal child node), tri_base (first triangle of this node's leaves), cm[0], cm[1]
 //   q2: qlo.x[0..7] qlo.y[0..7]   q3: qlo.z[0..7] qhi.x[0..7]   q4: qhi.y[0..7] qhi.z[0..7]      (8-bit grid coordinates)
-//   q5: cm[2..5]   q6: cm[6], cm[7], meta[0..3], meta[4..7]
+//   q5: cm[2..5]   q6: cm[6], cm[7], em, 0
 //       cm[s] = child mask of slot s: ((1 << count) - 1) << offset  leaf with 1..3 triangles at tri_base + offset
 //                                     1 << (24 + s)                  internal child (node = child_base + popc(imask below s))
 //                                     0                              empty slot
 //       so a hit ORs cm[s] into a 32-bit word: bits 0..23 = triangles of this node, bits 24..31 = internal children
 //       (the hit word of Ylitie, Karras, Laine 2017, precomputed per child instead of shifted together per visit).
-//       meta[s] = (unary count << 5) | offset: the builder's compact form of the same, kept for tools.
+//       em = the bits of that hit word whose child contains / whose triangle is an emitter (material.is_light): the
+//       emitter phase of the MIS query (QUERY 2 below) ANDs its hit word with it.
 // Child slots are assigned at build time by octant (slot bit k set = child on the + side of axis k), so
 // `slot ^ ray_octant` orders children front to back without sorting (Ylitie et al. 2017).
 //
@@ -89,11 +90,13 @@ HJ_DI uint32_t load_two23() { return *(const volatile uint32_t*)&c_two23; }
 // one lookup in a 2 KB shared-memory table. r01-p SASS had the masks assembled from 8 meta bytes with ~53 ALU-pipe
 // instructions (extract, shift, select) per node; the ALU pipe (PRMT, FMNMX, SHF, LOP3, SEL at one warp instruction
 // per 2 cycles) is what bounds the node test, so those moved into the node: 80 -> 112 B, -40 ALU instructions.
+template <bool EM>
 HJ_DI void node_boxes(const uint4* __restrict__ nodes, uint32_t node, const float3& o, const float3& idir, uint32_t oct,
-                      float tmin, float tcur, uint32_t k4b, const uint8_t* perm_row, uint2& ng, uint2& tg) {
+                      float tmin, float tcur, uint32_t k4b, const uint8_t* perm_row, bool em, uint2& ng, uint2& tg) {
     const uint4* N = nodes + HJ_NODE_QUADS * (size_t)node;
     const uint4 q0 = __ldg(N), q1 = __ldg(N + 1), q2 = __ldg(N + 2), q3 = __ldg(N + 3), q4 = __ldg(N + 4), q5 = __ldg(N + 5);
-    const uint2 q6 = __ldg((const uint2*)(N + 6));
+    uint4 q6;
+    if (EM) q6 = __ldg(N + 6); else { const uint2 t = __ldg((const uint2*)(N + 6)); q6 = make_uint4(t.x, t.y, 0u, 0u); }
     const float sx = __uint_as_float((q0.w & 0xffu) << 23), sy = __uint_as_float(((q0.w >> 8) & 0xffu) << 23),
                 sz = __uint_as_float(((q0.w >> 16) & 0xffu) << 23);
     const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
@@ -131,6 +134,7 @@ HJ_DI void node_boxes(const uint4* __restrict__ nodes, uint32_t node, const floa
             if (tn <= tf) hitmask |= cm[4 * h + j];      // empty slots have cm = 0
         }
     }
+    if (EM && em) hitmask &= q6.z;                 // emitter phase: only children that contain / triangles that are emitters
     ng = make_uint2(q1.x, ((uint32_t)perm_row[hitmask >> 24] << 24) | (q0.w >> 24));
     tg = make_uint2(q1.y, hitmask & 0x00ffffffu);
 }
@@ -180,10 +184,19 @@ struct TraceShared {
     float2 bary[HJ_TRACE_THREADS];                  // barycentrics of the best hit
     uint8_t perm[8][256];                           // octant permutation of the inner-child hit bits (fill_octant_perm)
     uint2 rring[HJ_TRACE_THREADS / 32][HJ_RCAP];    // pending leaf records: first triangle (leaf order), hit bits | owner lane << 24
+    unsigned long long key0[HJ_TRACE_THREADS];      // QUERY 2: the emitter phase's result = the key the occlusion phase starts from
 };
 
+// QUERY 0: closest hit. 1: any hit (occlusion). 2: "is the closest hit an emitter, and which" — the MIS emitter ray
+// (rt.h:383-420 uses its closest hit only if that is a light; anything else contributes nothing). Answered in two walks
+// of the same lane: (a) closest hit among EMITTERS only (hit words ANDed with the nodes' em bits: a few node visits),
+// giving the key (t_e, prim_e) or (tmax, none); (b) an any-hit walk for a key below it — smaller t, or the same t and a
+// lower primitive id, exactly the closest-hit order — which ends at the first such triangle. Result: Hit of the emitter /
+// miss (nothing at all: sky) / prim = HJ_HIT_BLOCKED. Same answer as QUERY 0 whenever that one's hit is an emitter or a miss.
+#define HJ_HIT_BLOCKED 0xfffffffeu
+
 // IO: uint32_t count; bool load(idx, o, d, tmin, tmax) (false: empty entry); void finish(const Hit&)
-template <bool ANY, bool COUNT, class IO>
+template <int QUERY, bool COUNT, class IO>
 HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next, TraceShared& sh, uint2* l_stack,
                            uint32_t& n_rays, uint32_t& n_nodes, uint32_t& n_tris, uint32_t* max_nodes, uint32_t* max_tris,
                            unsigned long long* diag = nullptr) {
@@ -197,6 +210,8 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
     float3 o = f3(0.0f), idir = f3(0.0f); uint32_t oct = 0; float tmin = 0.0f;
     uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u); int sp = 0;
     bool active = false, exhausted = false;
+    bool emph = false;                              // QUERY 2: this lane is in its emitter phase
+    constexpr bool ANY = QUERY == 1;
     uint32_t nn0 = 0, own_tris = 0;
     const uint32_t k4b = load_two23();
     fill_octant_perm(sh.perm);
@@ -205,11 +220,18 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
         // ---- lanes whose walk is over and whose queued pairs are all tested hand their result over (once per burst,
         //      so that the write-out runs several lanes wide)
         if (active && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u && (int32_t)(head - ticket) >= 0) {
-            const unsigned long long k = sh.key[tid]; const float2 b = sh.bary[tid];
-            Hit h; h.t = __uint_as_float((uint32_t)(k >> 32)); h.prim = (uint32_t)k; h.b1 = b.x; h.b2 = b.y;
-            io.finish(h);
-            n_rays++; active = false;
-            if (COUNT) { atomicMax(max_nodes, n_nodes - nn0); atomicMax(max_tris, own_tris); }
+            const unsigned long long k = sh.key[tid];
+            if (QUERY == 2 && emph) {               // emitter phase over: walk again from the root for anything in front of it
+                emph = false; sh.key0[tid] = k;
+                ng = make_uint2(0u, 0x80000000u);
+            } else {
+                const float2 b = sh.bary[tid];
+                Hit h; h.t = __uint_as_float((uint32_t)(k >> 32)); h.prim = (uint32_t)k; h.b1 = b.x; h.b2 = b.y;
+                if (QUERY == 2 && k != sh.key0[tid]) h.prim = HJ_HIT_BLOCKED;
+                io.finish(h);
+                n_rays++; active = false;
+                if (COUNT) { atomicMax(max_nodes, n_nodes - nn0); atomicMax(max_tris, own_tris); }
+            }
         }
         const uint32_t idle = __ballot_sync(FULL, !active);
         if (!exhausted && __popc(idle) >= REFILL_MIN) {
@@ -231,7 +253,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                     sh.bary[tid] = make_float2(0.0f, 0.0f);
                     ng = make_uint2(0u, 0x80000000u);     // the root, as the only inner hit of a virtual parent
                     tg = make_uint2(0u, 0u); sp = 0; ticket = head;
-                    active = true; nn0 = n_nodes; own_tris = 0;
+                    active = true; nn0 = n_nodes; own_tris = 0; emph = QUERY == 2;
                 }
             }
             if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
@@ -251,7 +273,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                     if (ng.y > 0x00ffffffu) { if (sp < HJ_SSTACK) sstack[sp * HJ_TRACE_THREADS] = ng; else l_stack[sp - HJ_SSTACK] = ng; sp++; }
                     if (COUNT) n_nodes++;
                     const float tcur = __uint_as_float((uint32_t)(sh.key[tid] >> 32));
-                    node_boxes(S.nodes, node, o, idir, oct, tmin, tcur, k4b, sh.perm[oct ^ 7u], ng, tg);
+                    node_boxes<QUERY == 2>(S.nodes, node, o, idir, oct, tmin, tcur, k4b, sh.perm[oct ^ 7u], emph, ng, tg);
                     did = true;
                 }
             }
@@ -335,6 +357,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
             }
             // ---- any hit ends an occlusion ray
             if (ANY && active && (uint32_t)sh.key[tid] != 0xffffffffu) { ng.y = 0u; tg.y = 0u; sp = 0; }
+            if (QUERY == 2 && active && !emph && sh.key[tid] != sh.key0[tid]) { ng.y = 0u; tg.y = 0u; sp = 0; }
         }
     }
     if (COUNT && diag && lane == 0) {

@@ -340,7 +340,9 @@ HJ_DI void finish_mis(const DevScene& S, const FrameK& F, const WfPtrs& P, uint3
     const float c1 = oq.w, ppdf = dq.w;
     const float4 Lq = P.L[slot];
     float3 L = f3(Lq);
-    if (h.prim != 0xffffffffu) {
+    if (h.prim == HJ_HIT_BLOCKED) {
+        // emitter-first query (MODE 3): something that is not a light is the closest hit — no contribution (rt.h:394)
+    } else if (h.prim != 0xffffffffu) {
         const float4 a3 = S.tri_attr[4 * (size_t)h.prim + 3];
         const DevMaterial& m = S.materials[__float_as_uint(a3.w)];
         if (m.is_light) {
@@ -364,7 +366,9 @@ HJ_DI void finish_mis(const DevScene& S, const FrameK& F, const WfPtrs& P, uint3
     P.L[slot] = f4(L, Lq.w + 1.0f);
 }
 
-// MODE 0: extend (closest hit), 1: shadow (any hit), 2: MIS emitter ray (closest hit).
+// MODE 0: extend (closest hit), 1: shadow (any hit), 2: MIS emitter ray (closest hit), 3: MIS emitter ray answered by the
+// emitter-first query (QUERY 2 of hj_trace.cuh: closest emitter, then any hit in front of it) — same contribution, and the
+// walk through the whole scene may stop at the first blocker instead of finding the nearest one.
 // The warp loop (dynamic ray fetch, node phases, pooled 32-wide triangle tests) is trace_warp_loop in hj_trace.cuh.
 template <int MODE>
 struct WfRayIO {
@@ -391,7 +395,8 @@ __global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace(DevScene S,
     const uint32_t n = MODE == 0 ? P.cnt->n_extend[cur] : (MODE == 1 ? P.cnt->n_shadow : P.cnt->n_mis);
     WfRayIO<MODE> io{S, F, P, MODE == 0 ? P.q_ext[cur] : (MODE == 1 ? P.q_shadow : P.q_mis), 0u};
     uint32_t nr = 0, nn = 0, nt = 0;
-    trace_warp_loop<MODE == 1, COUNT>(S, io, n, &P.cnt->next[MODE], sh, l_stack, nr, nn, nt, &P.cnt->max_nodes, &P.cnt->max_tris, P.cnt->diag[MODE]);
+    constexpr int QUERY = MODE == 1 ? 1 : (MODE == 3 ? 2 : 0), CTR = MODE == 3 ? 2 : MODE;
+    trace_warp_loop<QUERY, COUNT>(S, io, n, &P.cnt->next[CTR], sh, l_stack, nr, nn, nt, &P.cnt->max_nodes, &P.cnt->max_tris, P.cnt->diag[CTR]);
     warp_add64(MODE == 1 ? &P.cnt->rays_shadow : &P.cnt->rays_extend, nr);
     if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
 }
@@ -465,7 +470,7 @@ __global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace_batch(DevSc
     uint2 l_stack[HJ_STACK];
     BatchRayIO<ANY> io{rays, prim, tuv, 0u};
     uint32_t nr = 0, nn = 0, nt = 0;
-    trace_warp_loop<ANY, false>(S, io, n, cursor, sh, l_stack, nr, nn, nt, nullptr, nullptr);
+    trace_warp_loop<ANY ? 1 : 0, false>(S, io, n, cursor, sh, l_stack, nr, nn, nt, nullptr, nullptr);
 }
 
 int hj_trace_batch(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, uint32_t* prim_host, float* tuv_host) {
@@ -649,7 +654,10 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
             }
             if (fp->integrator == HJ_INTEGRATOR_MIS) {
                 mark_begin(0, ps);
-                if (count) k_trace<2, true><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
+                // the debug records hash the MIS ray's closest hit whatever it is: they need the plain closest-hit query
+                const bool efirst = c->opt_mis_emitter_first && !debug;
+                if (efirst) { if (count) k_trace<3, true><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur); else k_trace<3, false><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur); }
+                else if (count) k_trace<2, true><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
                 else k_trace<2, false><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
                 mark_end(ps);
                 launches++;

@@ -123,3 +123,38 @@ def test_furnace_energy_conservation(gpu):
         assert 0.85 < centre <= 1.0 + 1e-3, (rough, centre)
         want = Oracle(s).render(fp)
         assert np.sqrt(np.mean((col - want["color"][..., :3]) ** 2)) < 2e-3
+
+
+@pytest.mark.parametrize("which", ["cornell", "c2", "c3", "no_lights"])
+def test_mis_emitter_first_query_is_the_closest_hit_query(gpu, which):
+    """The MIS emitter ray (rt.h:383-420) uses its closest hit only if that is a light. The emitter-first query (closest
+    emitter, then any hit in front of it — the default outside debug_paths) must give bit-identical frames to the plain
+    closest-hit query, whose per-path radiance the tests above pin against the oracle."""
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if which == "cornell":
+        s = hj.load_npz(os.path.join(root, "tests", "golden", "cornelbox.npz")); s.set_sky((0.8, 0.8, 0.8)); depth = 8
+    elif which == "c2":
+        s = scenes.rtcamp_like(statue_subdiv=4, detail=0.08); depth = 10
+    elif which == "c3":
+        s = scenes.metaglass_room(subdiv=3); depth = 32
+    else:                                  # no emitter at all: the emitter phase ends at the root, sky hits still count
+        s = hj.load_npz(os.path.join(root, "tests", "golden", "cornelbox.npz")); s.set_sky((0.8, 0.8, 0.8)); depth = 6
+        for m in s.materials:
+            m["emission"] = (0.0, 0.0, 0.0); m["is_light"] = 0
+        s.finalize_lights()
+        assert s.light_prim_ids.size == 0
+    fp = hj.frame_params(s, 160, 90, 4, frame=2, max_depth=depth, integrator=abi.INTEGRATOR_MIS)
+    gpu.upload(s); gpu.build_accel()
+    out = []
+    for efirst in (0, 1):
+        gpu.set_option("mis_emitter_first", efirst)
+        gpu.render(fp)
+        out.append(gpu.readback(abi.AOV_ACCUM).copy())
+    gpu.set_option("mis_emitter_first", 1)
+    assert np.array_equal(out[0].view(np.uint32), out[1].view(np.uint32))
+    assert np.nansum(out[0][..., :3]) > 0
+    # and after a refit (the emitter marks are rebuilt with the boxes)
+    gpu.build_accel(mode=abi.ACCEL_REFIT)
+    gpu.render(fp)
+    assert np.array_equal(gpu.readback(abi.AOV_ACCUM).view(np.uint32), out[0].view(np.uint32))
