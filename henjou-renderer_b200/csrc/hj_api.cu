@@ -5,6 +5,7 @@
 // No exception crosses the boundary; there is no CPU path: without an sm_100 device hj_create fails.
 #include "hj_ctx.h"
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -43,6 +44,7 @@ int hj_create(hj_ctx** out, int device) {
     hj_ctx* c = new (std::nothrow) hj_ctx();
     if (!c) { g_create_err = "hj_create: out of host memory"; return HJ_ERR_OOM; }
     c->device = device;
+    if (const char* v = getenv("HJ_VERIFY_ACCEL")) c->opt_verify_accel = atoi(v) != 0;    // the test suite sets it
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess || (e = cudaEventCreate(&c->ev0)) != cudaSuccess ||
         (e = cudaEventCreate(&c->ev1)) != cudaSuccess) {
         g_create_err = cudaGetErrorString(e); delete c; return HJ_ERR_CUDA;
@@ -64,7 +66,7 @@ void hj_destroy(hj_ctx* c) {
                       &c->bvh.keys, &c->bvh.keys_alt, &c->bvh.vals, &c->bvh.vals_alt, &c->bvh.block_hist, &c->bvh.blo, &c->bvh.bhi, &c->bvh.left,
                       &c->bvh.right, &c->bvh.parent, &c->bvh.cnt, &c->bvh.flags, &c->bvh.p_cid[0], &c->bvh.p_cid[1], &c->bvh.p_lo[0], &c->bvh.p_lo[1],
                       &c->bvh.p_hi[0], &c->bvh.p_hi[1], &c->bvh.p_nn, &c->bvh.p_keep, &c->bvh.p_bcount, &c->bvh.bounds, &c->bvh.queue_a, &c->bvh.queue_b,
-                      &c->bvh.counters, &c->bvh.nodes, &c->bvh.btris,
+                      &c->bvh.counters, &c->bvh.verr, &c->bvh.nodes, &c->bvh.btris,
                       &c->aov_color, &c->aov_albedo, &c->aov_normal, &c->aov_rgba8, &c->aov_accum, &c->aov_path_rad, &c->aov_path_ids,
                       &c->aov_output, &c->aov_output_rgba8, &c->post_tmp[0], &c->post_tmp[1]};
     for (DevBuf* b : bufs) b->release();
@@ -91,6 +93,8 @@ int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
     else if (!strcmp(key, "pipelines")) { HJ_REQUIRE(c, value >= 1 && value <= HJ_MAX_PIPES, HJ_ERR_INVALID, "hj_set_option: pipelines must be 1..8"); c->opt_pipelines = (int)value; }
     else if (!strcmp(key, "builder")) { HJ_REQUIRE(c, value == 0 || value == 1, HJ_ERR_INVALID, "hj_set_option: builder must be 0 (LBVH) or 1 (PLOC)"); c->opt_builder = (int)value; c->bvh.have_topology = false; }
     else if (!strcmp(key, "leaf_max")) { HJ_REQUIRE(c, value >= 1 && value <= 3, HJ_ERR_INVALID, "hj_set_option: leaf_max must be 1..3"); c->opt_leaf_max = (int)value; }
+    else if (!strcmp(key, "leaf_split")) c->opt_leaf_split = value != 0;
+    else if (!strcmp(key, "verify_accel")) c->opt_verify_accel = value != 0;
     else if (!strcmp(key, "mis_emitter_first")) c->opt_mis_emitter_first = value != 0;
     else if (!strcmp(key, "denoise_iterations")) { HJ_REQUIRE(c, value >= 0 && value <= 8, HJ_ERR_INVALID, "hj_set_option: denoise_iterations must be 0..8"); c->opt_denoise_iterations = (int)value; }
     else if (!strncmp(key, "denoise_sigma_", 14)) {

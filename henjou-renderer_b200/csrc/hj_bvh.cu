@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(PLOC_THREADS) k_ploc_compact(int n, const uint
 
 // ---------------------------------------------------------------------------------------------- collapse to 8-wide
 struct CollapseArgs {
-    int n; uint32_t leaf_max;
+    int n; uint32_t leaf_max; int leaf_split;
     const uint32_t *left, *right, *cnt, *sorted;
     const float4 *blo, *bhi;
     const float4* tri_pos;
@@ -335,150 +335,235 @@ struct CollapseArgs {
 };
 
 HJ_DI uint32_t bn_count(const CollapseArgs& a, uint32_t id) { return id >= (uint32_t)(a.n - 1) ? 1u : a.cnt[id]; }
-// the (<= 3) leaves below a binary node, as indices into the Morton-sorted triangle order
-HJ_DI int bn_leaves(const CollapseArgs& a, uint32_t id, uint32_t out[4]) {
-    uint32_t st[4]; int sp = 0, n = 0;
-    st[sp++] = id;
-    while (sp) {
-        const uint32_t x = st[--sp];
-        if (x >= (uint32_t)(a.n - 1)) { if (n < 4) out[n++] = x - (uint32_t)(a.n - 1); }
-        else { st[sp++] = a.right[x]; st[sp++] = a.left[x]; }
-    }
-    return n;
+// the (<= 3) leaves below a binary node, left to right, as indices into the Morton-sorted triangle order. Written out
+// case by case so that the result lives in three registers (no local-memory stack, see k_collapse).
+HJ_DI uint32_t bn_leaves3(const CollapseArgs& a, uint32_t id, uint32_t& l0, uint32_t& l1, uint32_t& l2) {
+    const uint32_t first = (uint32_t)(a.n - 1);
+    l0 = l1 = l2 = 0u;
+    if (id >= first) { l0 = id - first; return 1u; }
+    const uint32_t l = a.left[id], r = a.right[id];
+    if (l < first) { l0 = a.left[l] - first; l1 = a.right[l] - first; l2 = r - first; return 3u; }      // ((x x) x)
+    if (r < first) { l0 = l - first; l1 = a.left[r] - first; l2 = a.right[r] - first; return 3u; }      // (x (x x))
+    l0 = l - first; l1 = r - first; return 2u;
 }
 HJ_DI float bn_area(const CollapseArgs& a, uint32_t id) {
     const float4 l = a.blo[id], h = a.bhi[id];
     const float dx = h.x - l.x, dy = h.y - l.y, dz = h.z - l.z;
     return dx * dy + dy * dz + dz * dx;
 }
+// grid exponent of one axis: the smallest power-of-two step with 255 steps covering [lo, hi]
+HJ_DI uint32_t grid_exponent(float lo, float hi) {
+    const float ext = hi - lo;
+    uint32_t e = 1;
+    if (ext > 0.0f) {
+        const uint32_t bits = __float_as_uint(ext / 255.0f);
+        e = (bits >> 23) & 0xffu;
+        if (bits & 0x7fffffu) e++;
+        if (e < 1u) e = 1u;
+    }
+    while (e < 254u && lo + 255.0f * __uint_as_float(e << 23) < hi) e++;
+    return e;
+}
+// conservative 8-bit grid coordinates of [clo, chi] on the grid (lo, scale)
+HJ_DI uint32_t grid_floor(float clo, float lo, float scale) {
+    int q = (int)floorf((clo - lo) / scale);
+    q = max(0, min(255, q));
+    while (q > 0 && lo + (float)q * scale > clo) q--;
+    return (uint32_t)q;
+}
+HJ_DI uint32_t grid_ceil(float chi, float lo, float scale) {
+    int q = (int)ceilf((chi - lo) / scale);
+    q = max(0, min(255, q));
+    while (q < 255 && lo + (float)q * scale < chi) q++;
+    return (uint32_t)q;
+}
 
 // One thread turns one binary subtree root into one wide node: repeatedly opens the child with the largest
 // surface area until 8 children (or nothing left to open), orders the children into octant slots, quantises
 // their boxes conservatively on the node's 8-bit grid and copies the triangles of its leaf children.
-__global__ void k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32_t n_in, uint2* __restrict__ qout) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+//
+// Per-thread state that is indexed dynamically (the 8 children and their boxes) lives in SHARED memory, everything else
+// in scalar registers and bit fields. r01-w: the earlier form kept ~600 B of dynamically indexed local arrays; a small
+// source change made nvcc 12.9 produce a kernel whose child boxes were overwritten while still live (children's
+// quantised boxes no longer contained their triangles -> missed hits). k_verify (option verify_accel) checks the result.
+#define COLLAPSE_THREADS 128
+__global__ void __launch_bounds__(COLLAPSE_THREADS) k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32_t n_in, uint2* __restrict__ qout) {
+    __shared__ uint32_t s_ch[8][COLLAPSE_THREADS];
+    __shared__ float s_lo[3][8][COLLAPSE_THREADS], s_hi[3][8][COLLAPSE_THREADS];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t i = blockIdx.x * blockDim.x + tid;
     if (i >= n_in) return;
     const uint2 work = qin[i];
-    uint32_t ch[8]; int nc = 1; ch[0] = work.x;
+    const uint32_t first_leaf = (uint32_t)(a.n - 1);
+    // Phase 0 opens the child with the largest surface area among those holding more than leaf_max triangles. Phase 1
+    // (leaf_split): slots left over -> split multi-triangle leaf children too, largest box first: the node test looks at
+    // all 8 slots anyway, so tighter per-triangle boxes cost nothing and save triangle tests.
+    int nc = 1; s_ch[0][tid] = work.x;
+    bool split = false;
     while (nc < 8) {
         int best = -1; float ba = -1.0f;
         for (int k = 0; k < nc; k++) {
-            const uint32_t id = ch[k];
-            const bool open = id < (uint32_t)(a.n - 1) && (bn_count(a, id) > a.leaf_max || nc == 1);
+            const uint32_t id = s_ch[k][tid];
+            const bool open = id < first_leaf && (split || bn_count(a, id) > a.leaf_max || nc == 1);
             if (open) { const float ar = bn_area(a, id); if (ar > ba) { ba = ar; best = k; } }
         }
-        if (best < 0) break;
-        const uint32_t id = ch[best];
-        ch[best] = a.left[id]; ch[nc++] = a.right[id];
+        if (best < 0) {
+            if (split || !a.leaf_split) break;
+            split = true; continue;
+        }
+        const uint32_t id = s_ch[best][tid];
+        s_ch[best][tid] = a.left[id]; s_ch[nc][tid] = a.right[id]; nc++;
     }
-    // node box
-    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-    float clo[8][3], chi[8][3];
+    // child boxes and the node box
+    float lox = FLT_MAX, loy = FLT_MAX, loz = FLT_MAX, hix = -FLT_MAX, hiy = -FLT_MAX, hiz = -FLT_MAX;
     for (int k = 0; k < nc; k++) {
-        const float4 l = a.blo[ch[k]], h = a.bhi[ch[k]];
-        clo[k][0] = l.x; clo[k][1] = l.y; clo[k][2] = l.z; chi[k][0] = h.x; chi[k][1] = h.y; chi[k][2] = h.z;
-        for (int ax = 0; ax < 3; ax++) { lo[ax] = fminf(lo[ax], clo[k][ax]); hi[ax] = fmaxf(hi[ax], chi[k][ax]); }
+        const uint32_t id = s_ch[k][tid];
+        const float4 l = a.blo[id], h = a.bhi[id];
+        s_lo[0][k][tid] = l.x; s_lo[1][k][tid] = l.y; s_lo[2][k][tid] = l.z;
+        s_hi[0][k][tid] = h.x; s_hi[1][k][tid] = h.y; s_hi[2][k][tid] = h.z;
+        lox = fminf(lox, l.x); loy = fminf(loy, l.y); loz = fminf(loz, l.z);
+        hix = fmaxf(hix, h.x); hiy = fmaxf(hiy, h.y); hiz = fmaxf(hiz, h.z);
     }
-    // octant slots: greedy assignment maximising (child centre - node centre) . (+-1,+-1,+-1)
-    int slot_of[8]; bool slot_used[8], child_done[8];
-    for (int k = 0; k < 8; k++) { slot_used[k] = false; child_done[k] = false; slot_of[k] = -1; }
+    // octant slots: greedy assignment maximising (child centre - node centre) . (+-1,+-1,+-1).
+    // slot_of: nibble k = slot of child k; child_in: nibble s = child in slot s (0xf: empty)
+    uint32_t slot_of = 0u, slots_used = 0u, done = 0u;
+    const float ncx = (lox + hix) * 0.5f, ncy = (loy + hiy) * 0.5f, ncz = (loz + hiz) * 0.5f;
     for (int round = 0; round < nc; round++) {
         float bc = -FLT_MAX; int bk = -1, bs = -1;
         for (int k = 0; k < nc; k++) {
-            if (child_done[k]) continue;
-            float c[3];
-            for (int ax = 0; ax < 3; ax++) c[ax] = (clo[k][ax] + chi[k][ax]) * 0.5f - (lo[ax] + hi[ax]) * 0.5f;
-            for (int s = 0; s < 8; s++) {
-                if (slot_used[s]) continue;
-                const float cost = ((s & 1) ? c[0] : -c[0]) + ((s & 2) ? c[1] : -c[1]) + ((s & 4) ? c[2] : -c[2]);
-                if (cost > bc) { bc = cost; bk = k; bs = s; }
+            if (done & (1u << k)) continue;
+            const float c0 = (s_lo[0][k][tid] + s_hi[0][k][tid]) * 0.5f - ncx, c1 = (s_lo[1][k][tid] + s_hi[1][k][tid]) * 0.5f - ncy,
+                        c2 = (s_lo[2][k][tid] + s_hi[2][k][tid]) * 0.5f - ncz;
+            for (int sl = 0; sl < 8; sl++) {
+                if (slots_used & (1u << sl)) continue;
+                const float cost = ((sl & 1) ? c0 : -c0) + ((sl & 2) ? c1 : -c1) + ((sl & 4) ? c2 : -c2);
+                if (cost > bc) { bc = cost; bk = k; bs = sl; }
             }
         }
-        slot_of[bk] = bs; slot_used[bs] = true; child_done[bk] = true;
+        if (bk < 0) {                                    // only with non-finite boxes: first free child into the first free slot
+            bk = __ffs((int)(~done & ((1u << nc) - 1u))) - 1; bs = __ffs((int)(~slots_used & 0xffu)) - 1;
+        }
+        slot_of |= (uint32_t)bs << (4 * bk); slots_used |= 1u << bs; done |= 1u << bk;
     }
-    int child_in_slot[8];
-    for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
-    for (int k = 0; k < nc; k++) child_in_slot[slot_of[k]] = k;
+    uint32_t child_in = 0xffffffffu;
+    for (int k = 0; k < nc; k++) {
+        const uint32_t sl = (slot_of >> (4 * k)) & 7u;
+        child_in = (child_in & ~(0xfu << (4u * sl))) | ((uint32_t)k << (4u * sl));
+    }
     // grid: per axis the smallest power-of-two step with 255 steps covering the node
-    uint32_t eb[3]; float scale[3];
-    for (int ax = 0; ax < 3; ax++) {
-        const float ext = hi[ax] - lo[ax];
-        uint32_t e = 1;
-        if (ext > 0.0f) {
-            const uint32_t bits = __float_as_uint(ext / 255.0f);
-            e = (bits >> 23) & 0xffu;
-            if (bits & 0x7fffffu) e++;
-            if (e < 1u) e = 1u;
-        }
-        while (e < 254u && lo[ax] + 255.0f * __uint_as_float(e << 23) < hi[ax]) e++;
-        eb[ax] = e; scale[ax] = __uint_as_float(e << 23);
-    }
+    const uint32_t ebx = grid_exponent(lox, hix), eby = grid_exponent(loy, hiy), ebz = grid_exponent(loz, hiz);
+    const float scx = __uint_as_float(ebx << 23), scy = __uint_as_float(eby << 23), scz = __uint_as_float(ebz << 23);
+    uint4* N = a.nodes + HJ_NODE_QUADS * (size_t)work.y;
+    uint32_t* Nw = (uint32_t*)N;
     uint32_t imask = 0, n_int = 0, n_tri = 0, em_word = 0;
-    uint32_t meta[8], qlo[3][8], qhi[3][8];
-    for (int s = 0; s < 8; s++) {
-        meta[s] = 0;
-        for (int ax = 0; ax < 3; ax++) { qlo[ax][s] = 255; qhi[ax][s] = 0; }
-        const int k = child_in_slot[s];
-        if (k < 0) continue;
-        const uint32_t id = ch[k];
-        const uint32_t cnt = bn_count(a, id);
-        if (id < (uint32_t)(a.n - 1) && cnt > a.leaf_max) {
-            imask |= 1u << s; n_int++; meta[s] = (1u << 5) | (24u + (uint32_t)s);
-            if (a.blo[id].w > 0.0f) em_word |= 1u << (24 + s);
-        } else {
-            meta[s] = (((1u << cnt) - 1u) << 5) | n_tri;
-            if (a.blo[id].w > 0.0f) {                     // which of its (<= 3) triangles emit
-                uint32_t lv[4];
-                const uint32_t m = (uint32_t)bn_leaves(a, id, lv);
-                for (uint32_t j = 0; j < m; j++) if (a.blo[(uint32_t)(a.n - 1) + lv[j]].w > 0.0f) em_word |= 1u << (n_tri + j);
+    unsigned long long qlx = 0, qly = 0, qlz = 0, qhx = 0, qhy = 0, qhz = 0;       // byte s = grid coordinate of slot s
+    for (int sl = 0; sl < 8; sl++) {
+        const uint32_t k = (child_in >> (4 * sl)) & 0xfu;
+        // child mask of slot sl: where its hit lands in the traversal's 32-bit hit word (bits 0..23 triangles of this node,
+        // bit 24+s inner child in slot s; the ray-octant permutation of the inner bits is applied by the traversal)
+        uint32_t cm = 0u, q[6] = {255u, 255u, 255u, 0u, 0u, 0u};
+        if (k != 0xfu) {
+            const uint32_t id = s_ch[k][tid];
+            const uint32_t cnt = bn_count(a, id);
+            const bool emits = a.blo[id].w > 0.0f;
+            if (id < first_leaf && cnt > a.leaf_max) {
+                imask |= 1u << sl; n_int++; cm = 1u << (24 + sl);
+                if (emits) em_word |= cm;
+            } else {
+                cm = ((1u << cnt) - 1u) << n_tri;
+                if (emits) {                              // which of its (<= 3) triangles emit
+                    uint32_t l0, l1, l2;
+                    const uint32_t m = bn_leaves3(a, id, l0, l1, l2);
+                    if (a.blo[first_leaf + l0].w > 0.0f) em_word |= 1u << n_tri;
+                    if (m > 1u && a.blo[first_leaf + l1].w > 0.0f) em_word |= 1u << (n_tri + 1u);
+                    if (m > 2u && a.blo[first_leaf + l2].w > 0.0f) em_word |= 1u << (n_tri + 2u);
+                }
+                n_tri += cnt;
             }
-            n_tri += cnt;
+            q[0] = grid_floor(s_lo[0][k][tid], lox, scx); q[1] = grid_floor(s_lo[1][k][tid], loy, scy); q[2] = grid_floor(s_lo[2][k][tid], loz, scz);
+            q[3] = grid_ceil(s_hi[0][k][tid], lox, scx); q[4] = grid_ceil(s_hi[1][k][tid], loy, scy); q[5] = grid_ceil(s_hi[2][k][tid], loz, scz);
         }
-        for (int ax = 0; ax < 3; ax++) {
-            int ql = (int)floorf((clo[k][ax] - lo[ax]) / scale[ax]);
-            ql = max(0, min(255, ql));
-            while (ql > 0 && lo[ax] + (float)ql * scale[ax] > clo[k][ax]) ql--;
-            int qh = (int)ceilf((chi[k][ax] - lo[ax]) / scale[ax]);
-            qh = max(0, min(255, qh));
-            while (qh < 255 && lo[ax] + (float)qh * scale[ax] < chi[k][ax]) qh++;
-            qlo[ax][s] = (uint32_t)ql; qhi[ax][s] = (uint32_t)qh;
-        }
+        const int sh = 8 * sl;
+        qlx |= (unsigned long long)q[0] << sh; qly |= (unsigned long long)q[1] << sh; qlz |= (unsigned long long)q[2] << sh;
+        qhx |= (unsigned long long)q[3] << sh; qhy |= (unsigned long long)q[4] << sh; qhz |= (unsigned long long)q[5] << sh;
+        Nw[sl < 2 ? 6 + sl : 18 + sl] = cm;               // cm[0..1] = q1.zw, cm[2..5] = q5, cm[6..7] = q6.xy
     }
     const uint32_t child_base = n_int ? atomicAdd(&a.counters[0], n_int) : 0u;
     const uint32_t tri_base = n_tri ? atomicAdd(&a.counters[1], n_tri) : 0u;
-    // write the node
-    auto pack4 = [](const uint32_t* v) { return v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24); };
-    uint4* N = a.nodes + HJ_NODE_QUADS * (size_t)work.y;
-    N[0] = make_uint4(__float_as_uint(lo[0]), __float_as_uint(lo[1]), __float_as_uint(lo[2]), eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24));
-    // child masks: where a hit of slot s lands in the traversal's 32-bit hit word (bits 0..23 triangles of this node,
-    // bit 24+s inner child in slot s; the ray-octant permutation of the inner bits is applied by the traversal)
-    uint32_t cm[8];
-    for (int s = 0; s < 8; s++) cm[s] = (imask & (1u << s)) ? (1u << (24 + s)) : ((meta[s] >> 5) << (meta[s] & 31u));
-    N[1] = make_uint4(child_base, tri_base, cm[0], cm[1]);
-    N[2] = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
-    N[3] = make_uint4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
-    N[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
-    N[5] = make_uint4(cm[2], cm[3], cm[4], cm[5]);
-    N[6] = make_uint4(cm[6], cm[7], em_word, 0u);
-    // children: queue the internal ones (contiguous, in slot order), copy the triangles of the leaves
+    N[0] = make_uint4(__float_as_uint(lox), __float_as_uint(loy), __float_as_uint(loz), ebx | (eby << 8) | (ebz << 16) | (imask << 24));
+    Nw[4] = child_base; Nw[5] = tri_base;
+    N[2] = make_uint4((uint32_t)qlx, (uint32_t)(qlx >> 32), (uint32_t)qly, (uint32_t)(qly >> 32));
+    N[3] = make_uint4((uint32_t)qlz, (uint32_t)(qlz >> 32), (uint32_t)qhx, (uint32_t)(qhx >> 32));
+    N[4] = make_uint4((uint32_t)qhy, (uint32_t)(qhy >> 32), (uint32_t)qhz, (uint32_t)(qhz >> 32));
+    Nw[26] = em_word; Nw[27] = 0u;
+    // children: queue the internal ones (contiguous, in slot order), copy the triangles of the leaves (same order as above)
     const uint32_t qbase = n_int ? atomicAdd(&a.counters[2], n_int) : 0u;
-    uint32_t r = 0;
-    for (int s = 0; s < 8; s++) {
-        const int k = child_in_slot[s];
-        if (k < 0) continue;
-        if (imask & (1u << s)) { qout[qbase + r] = make_uint2(ch[k], child_base + r); r++; }
+    uint32_t r = 0, off = 0;
+    for (int sl = 0; sl < 8; sl++) {
+        const uint32_t k = (child_in >> (4 * sl)) & 0xfu;
+        if (k == 0xfu) continue;
+        const uint32_t id = s_ch[k][tid];
+        if (imask & (1u << sl)) { qout[qbase + r] = make_uint2(id, child_base + r); r++; }
         else {
-            uint32_t lv[4];
-            const uint32_t cnt = (uint32_t)bn_leaves(a, ch[k], lv), off = meta[s] & 31u;
+            uint32_t l0, l1, l2;
+            const uint32_t cnt = bn_leaves3(a, id, l0, l1, l2);
             for (uint32_t j = 0; j < cnt; j++) {
-                const uint32_t prim = a.sorted[lv[j]];
+                const uint32_t prim = a.sorted[j == 0u ? l0 : (j == 1u ? l1 : l2)];
                 const float4* P = a.tri_pos + 3 * (size_t)prim;
                 float4* T = a.btris + 3 * (size_t)(tri_base + off + j);
                 float4 v0 = P[0]; v0.w = __uint_as_float(prim);
                 T[0] = v0; T[1] = P[1]; T[2] = P[2];
             }
+            off += cnt;
         }
     }
+}
+
+// option verify_accel: every leaf triangle inside its slot's decoded box, every internal child's origin inside too, child masks
+// disjoint, every primitive in exactly one leaf (error bits in err[0], count of primitives not seen once in err[1])
+__global__ void k_verify(const uint4* __restrict__ nodes, const float4* __restrict__ btris, uint32_t n_nodes, uint32_t n_tris, uint32_t* seen, uint32_t* err) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    const uint4* N = nodes + HJ_NODE_QUADS * (size_t)i;
+    const uint4 q0 = N[0], q1 = N[1], q2 = N[2], q3 = N[3], q4 = N[4], q5 = N[5], q6 = N[6];
+    const float lo[3] = {__uint_as_float(q0.x), __uint_as_float(q0.y), __uint_as_float(q0.z)};
+    const float sc[3] = {__uint_as_float((q0.w & 0xffu) << 23), __uint_as_float(((q0.w >> 8) & 0xffu) << 23), __uint_as_float(((q0.w >> 16) & 0xffu) << 23)};
+    const uint32_t imask = q0.w >> 24;
+    const uint32_t cm[8] = {q1.z, q1.w, q5.x, q5.y, q5.z, q5.w, q6.x, q6.y};
+    const uint32_t ql[3][2] = {{q2.x, q2.y}, {q2.z, q2.w}, {q3.x, q3.y}}, qh[3][2] = {{q3.z, q3.w}, {q4.x, q4.y}, {q4.z, q4.w}};
+    uint32_t tri_union = 0;
+    for (int s = 0; s < 8; s++) {
+        float blo[3], bhi[3];
+        for (int ax = 0; ax < 3; ax++) {
+            blo[ax] = lo[ax] + (float)((ql[ax][s >> 2] >> (8 * (s & 3))) & 0xffu) * sc[ax];
+            bhi[ax] = lo[ax] + (float)((qh[ax][s >> 2] >> (8 * (s & 3))) & 0xffu) * sc[ax];
+        }
+        if (imask & (1u << s)) {
+            if (cm[s] != (1u << (24 + s))) atomicOr(err, 16u);
+            const uint32_t child = q1.x + __popc(imask & ((1u << s) - 1u));
+            if (child >= n_nodes) { atomicOr(err, 32u); continue; }
+            const uint4 c0 = nodes[HJ_NODE_QUADS * (size_t)child];
+            const float co[3] = {__uint_as_float(c0.x), __uint_as_float(c0.y), __uint_as_float(c0.z)};
+            for (int ax = 0; ax < 3; ax++) if (co[ax] < blo[ax] || co[ax] > bhi[ax]) atomicOr(err, 64u);
+        } else if (cm[s]) {
+            if (cm[s] & tri_union) atomicOr(err, 128u);
+            tri_union |= cm[s];
+            for (uint32_t m = cm[s]; m; m &= m - 1u) {
+                const uint32_t t = q1.y + (uint32_t)__ffs((int)m) - 1u;
+                if (t >= n_tris) { atomicOr(err, 256u); continue; }
+                const float4 v0 = btris[3 * (size_t)t], v1 = btris[3 * (size_t)t + 1], v2 = btris[3 * (size_t)t + 2];
+                const uint32_t prim = __float_as_uint(v0.w);
+                if (prim >= n_tris) { atomicOr(err, 512u); continue; }
+                atomicAdd(&seen[prim], 1u);
+                const float p[3][3] = {{v0.x, v0.y, v0.z}, {v1.x, v1.y, v1.z}, {v2.x, v2.y, v2.z}};
+                for (int v = 0; v < 3; v++) for (int ax = 0; ax < 3; ax++) if (p[v][ax] < blo[ax] || p[v][ax] > bhi[ax]) atomicOr(err, 1024u);
+            }
+        }
+    }
+}
+__global__ void k_verify_seen(const uint32_t* seen, uint32_t n, uint32_t* err) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && seen[i] != 1u) { atomicOr(err, 2048u); atomicAdd(err + 1, 1u); }
 }
 
 // ---------------------------------------------------------------------------------------------- host driver
@@ -566,7 +651,7 @@ int hj_bvh_build(hj_ctx* c, int mode) {
     HJ_CUDA(c, cudaMemcpyAsync(B.counters.p, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, st));
     HJ_CUDA(c, cudaMemcpyAsync(B.queue_a.p, &root, sizeof root, cudaMemcpyHostToDevice, st));
     CollapseArgs a;
-    a.n = (int)n; a.leaf_max = (uint32_t)c->opt_leaf_max;
+    a.n = (int)n; a.leaf_max = (uint32_t)c->opt_leaf_max; a.leaf_split = c->opt_leaf_split;
     a.left = B.left.as<uint32_t>(); a.right = B.right.as<uint32_t>(); a.cnt = B.cnt.as<uint32_t>();
     a.sorted = B.vals.as<uint32_t>(); a.blo = B.blo.as<float4>(); a.bhi = B.bhi.as<float4>(); a.tri_pos = c->S.tri_pos;
     a.nodes = B.nodes.as<uint4>(); a.btris = B.btris.as<float4>(); a.counters = B.counters.as<uint32_t>();
@@ -574,7 +659,7 @@ int hj_bvh_build(hj_ctx* c, int mode) {
     uint32_t n_in = 1, depth = 0, cnt[4];
     while (n_in) {
         HJ_CUDA(c, cudaMemsetAsync(a.counters + 2, 0, 4, st));
-        k_collapse<<<cdiv(n_in, 128), 128, 0, st>>>(a, qi, n_in, qo);
+        k_collapse<<<cdiv(n_in, COLLAPSE_THREADS), COLLAPSE_THREADS, 0, st>>>(a, qi, n_in, qo);
         HJ_CUDA(c, cudaMemcpyAsync(cnt, a.counters, sizeof cnt, cudaMemcpyDeviceToHost, st));
         HJ_CUDA(c, cudaStreamSynchronize(st));
         n_in = cnt[2]; std::swap(qi, qo); depth++;
@@ -584,6 +669,19 @@ int hj_bvh_build(hj_ctx* c, int mode) {
     HJ_CUDA(c, cudaEventSynchronize(c->ev1));
     HJ_CUDA(c, cudaGetLastError());
     float ms = 0; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    if (c->opt_verify_accel) {      // structural check of the wide BVH (k_verify); the tests switch it on
+        uint32_t h[2] = {0, 0};
+        HJ_CUDA(c, B.verr.reserve(8));
+        HJ_CUDA(c, cudaMemsetAsync(B.flags.p, 0, (size_t)n * 4, st)); HJ_CUDA(c, cudaMemsetAsync(B.verr.p, 0, 8, st));
+        k_verify<<<cdiv(cnt[0], 128), 128, 0, st>>>(B.nodes.as<uint4>(), B.btris.as<float4>(), cnt[0], n, B.flags.as<uint32_t>(), B.verr.as<uint32_t>());
+        k_verify_seen<<<cdiv(n, 256), 256, 0, st>>>(B.flags.as<uint32_t>(), n, B.verr.as<uint32_t>());
+        HJ_CUDA(c, cudaMemcpyAsync(h, B.verr.p, 8, cudaMemcpyDeviceToHost, st));
+        HJ_CUDA(c, cudaStreamSynchronize(st));
+        if (h[0]) {
+            char b[200]; snprintf(b, sizeof b, "hj_accel_build: verify_accel found an inconsistent BVH (error bits 0x%x, %u primitives not in exactly one leaf)", h[0], h[1]);
+            c->err = b; return HJ_ERR_INVALID;
+        }
+    }
     if (cnt[1] != n) { c->err = "hj_accel_build: internal error, leaf triangles != scene triangles"; return HJ_ERR_INVALID; }
     if (2 * depth > HJ_STACK) {
         char b[160]; snprintf(b, sizeof b, "hj_accel_build: wide BVH depth %u exceeds the traversal stack (%d)", depth, HJ_STACK);

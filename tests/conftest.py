@@ -4,6 +4,9 @@ import sys
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# every hj_accel_build of the test suite also runs the structural BVH check (k_verify, option verify_accel): each leaf
+# triangle inside its slot's decoded box, child masks disjoint, every primitive in exactly one leaf
+os.environ.setdefault("HJ_VERIFY_ACCEL", "1")
 for p in (ROOT, os.path.join(ROOT, "tests")):
     if p not in sys.path:
         sys.path.insert(0, p)

@@ -106,6 +106,11 @@ def test_c5_many_triangles_and_builders(gpu):
             p, t = gpu.trace(rays[:20000])
             assert np.array_equal(p, p0[:20000]) and np.array_equal(t, t0[:20000])
         gpu.set_option("leaf_max", 3)
+        # leaf_split off: multi-triangle leaves keep one box even when the wide node has free slots
+        gpu.set_option("leaf_split", 0); gpu.build_accel()
+        p, t = gpu.trace(rays[:20000])
+        assert np.array_equal(p, p0[:20000]) and np.array_equal(t, t0[:20000])
+        gpu.set_option("leaf_split", 1)
     gpu.set_option("builder", 0)
     assert (p0 != 0xffffffff).mean() > 0.5
 
