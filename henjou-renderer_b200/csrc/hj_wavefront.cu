@@ -27,6 +27,7 @@ struct WfCounters {
 
 struct FrameK {
     uint32_t W, H, WH, spp, frame, sample_begin;
+    uint32_t pix0, npix;      // this pass covers pixels [pix0, pix0 + npix) of its samples: slot = s_local * npix + (pixel - pix0)
     float3 cpos, cdir, cup, cright; float cf, ibl;
     int integrator, max_depth, tonemap, jitter, debug;
 };
@@ -72,7 +73,7 @@ HJ_DI bool roulette(float3& thr, Sampler& st) {
 __global__ void __launch_bounds__(WF_THREADS) k_raygen(FrameK F, WfPtrs P, uint32_t s0, uint32_t n_slots) {
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_slots; slot += stride) {
-        const uint32_t pix = slot % F.WH, s = s0 + slot / F.WH;
+        const uint32_t pix = F.pix0 + slot % F.npix, s = s0 + slot / F.npix;
         const uint32_t x = pix % F.W, y = pix / F.W;
         Sampler st; st.n_spp = s; st.scramble = F.frame; st.depth = 0; st.image_idx = pix;
         float jx = 0.0f, jy = 0.0f;
@@ -177,8 +178,8 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SURF_MINB) k_surface(DevScene S
         if (slot != 0xffffffffu) {
             const float4 hq = P.hit[slot];
             const uint32_t prim = __float_as_uint(hq.w);
-            const uint32_t pix = slot % F.WH;
-            const bool first_sample = (depth == 0 && s0 + slot / F.WH == 0);
+            const uint32_t pix = F.pix0 + slot % F.npix;
+            const bool first_sample = (depth == 0 && s0 + slot / F.npix == 0);
             if (prim == 0xffffffffu) {                               // __miss__ms (D6); AOVs stay 0 (raygen wrote them)
                 if (INTEG == HJ_INTEGRATOR_PT || depth == 0) {
                     const float3 em = sky_radiance(S, f3(P.ray_d[slot]), F.ibl);
@@ -220,7 +221,7 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_NEE_MINB) k_nee(DevScene S, Fra
         if (slot != 0xffffffffu) {
             const Surface prd = load_surface(P, slot);
             const float3 d = f3(P.ray_d[slot]), thr = f3(P.thr[slot]);
-            Sampler st; st.n_spp = s0 + slot / F.WH; st.scramble = F.frame; st.image_idx = slot % F.WH; st.depth = P.rng[slot];
+            Sampler st; st.n_spp = s0 + slot / F.npix; st.scramble = F.frame; st.image_idx = F.pix0 + slot % F.npix; st.depth = P.rng[slot];
             Disney bsdf; bsdf.init(prd);
             float3 t, b; const float3 nrm = prd.normal;
             onb(nrm, t, b);
@@ -271,7 +272,7 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S
             const Surface prd = load_surface(P, slot);
             const float3 d = f3(P.ray_d[slot]);
             float3 thr = f3(P.thr[slot]);
-            Sampler st; st.n_spp = s0 + slot / F.WH; st.scramble = F.frame; st.image_idx = slot % F.WH; st.depth = P.rng[slot];
+            Sampler st; st.n_spp = s0 + slot / F.npix; st.scramble = F.frame; st.image_idx = F.pix0 + slot % F.npix; st.depth = P.rng[slot];
             if (INTEG != HJ_INTEGRATOR_PT && S.n_lights >= 1) st.depth += 2;     // light pick + barycentrics (light_sample.h:18,60)
             float3 t, b; const float3 nrm = prd.normal;
             onb(nrm, t, b);
@@ -415,11 +416,12 @@ __global__ void k_swap_queues(WfCounters* c, int cur) {
 // end of a pass: per pixel, add the pass's samples in sample order (same float addition order as the
 // reference's spp loop), and export the per-path debug records
 __global__ void k_accumulate(FrameK F, WfPtrs P, float4* accum, uint32_t s0, uint32_t n_samples, float4* path_rad, uint2* path_ids) {
-    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
-    if (pix >= F.WH) return;
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= F.npix) return;
+    const uint32_t pix = F.pix0 + idx;
     float4 a = accum[pix];
     for (uint32_t s = 0; s < n_samples; s++) {
-        const size_t slot = (size_t)s * F.WH + pix;
+        const size_t slot = (size_t)s * F.npix + idx;
         const float4 L = P.L[slot];
         a.x += L.x; a.y += L.y; a.z += L.z; a.w += 1.0f;
         if (F.debug) {
@@ -576,9 +578,23 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     }
     uint32_t spass = (uint32_t)(target / WH); if (spass < 1) spass = 1; if (spass > ns && ns) spass = ns;
     if (spass * WH > 0xfffffff0ull) spass = (uint32_t)(0xfffffff0ull / WH);
-    const uint32_t n_passes = ns ? (ns + spass - 1) / spass : 0;
+    const uint32_t n_spasses = ns ? (ns + spass - 1) / spass : 0;
+    // Few samples per frame (the real-time C4 case: 1-3 spp under the fps budget) leave pipelines idle, and every bounce of a
+    // lone pass ends in the tail of its longest rays. Such frames are also cut into pixel bands so that all pipelines have
+    // a pass: band = a contiguous pixel range of the pass's samples, at least 128 Ki paths.
+    uint32_t bands = 1;
+    if (!timed && n_spasses && n_spasses < (uint32_t)np) {
+        bands = (uint32_t)np / n_spasses;
+        const uint64_t most = std::max<uint64_t>(1, ((uint64_t)spass * WH) >> 17);
+        if (bands > most) bands = (uint32_t)most;
+    }
+    if (c->opt_bands > 0) bands = (uint32_t)c->opt_bands;
+    if (bands > WH) bands = (uint32_t)WH;
+    const uint32_t band_pix = (uint32_t)((WH + bands - 1) / bands);
+    bands = (uint32_t)((WH + band_pix - 1) / band_pix);
+    const uint32_t n_passes = n_spasses * bands;
     if ((uint32_t)np > n_passes) np = (int)std::max(1u, n_passes);
-    const uint32_t cap = (uint32_t)(spass * WH);
+    const uint32_t cap = (uint32_t)((uint64_t)spass * band_pix);
     for (int p = 0; p < np; p++) { int rc = wf_reserve(c, c->wf[p], cap, fp->integrator == HJ_INTEGRATOR_MIS, debug); if (rc) return rc; }
     c->n_pipes_used = np;
     const size_t fb = (size_t)WH * sizeof(float4);
@@ -593,6 +609,7 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     }
     FrameK F;
     F.W = W; F.H = H; F.WH = (uint32_t)WH; F.spp = fp->spp; F.frame = fp->frame; F.sample_begin = fp->sample_begin;
+    F.pix0 = 0; F.npix = (uint32_t)WH;
     F.cpos = make_float3(fp->camera_pos[0], fp->camera_pos[1], fp->camera_pos[2]);
     F.cdir = make_float3(fp->camera_dir[0], fp->camera_dir[1], fp->camera_dir[2]);
     F.cup = make_float3(fp->camera_up[0], fp->camera_up[1], fp->camera_up[2]);
@@ -626,12 +643,16 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     for (int p = 0; p < np; p++) HJ_CUDA(c, cudaStreamWaitEvent(c->wf[p].stream, c->ev_frame, 0));
     cudaEvent_t prev_acc = nullptr;
     uint32_t pass = 0;
-    for (uint32_t s0 = fp->sample_begin; s0 < fp->sample_end; s0 += spass, pass++) {
+    const FrameK F_frame = F;
+    for (uint32_t s0 = fp->sample_begin; s0 < fp->sample_end; s0 += spass)
+    for (uint32_t band = 0; band < bands; band++, pass++) {
         WavefrontState& w = c->wf[pass % np];
+        FrameK F = F_frame;
+        F.pix0 = band * band_pix; F.npix = std::min(band_pix, (uint32_t)WH - F.pix0);
         cudaStream_t ps = w.stream;
         const WfPtrs P = wf_ptrs(c, w);
         const uint32_t nsamp = std::min(spass, fp->sample_end - s0);
-        const uint32_t nslots = (uint32_t)(nsamp * WH);
+        const uint32_t nslots = (uint32_t)((uint64_t)nsamp * F.npix);
         k_reset_queues<<<1, 1, 0, ps>>>(P.cnt, nslots, 1);
         k_raygen<<<grid, WF_THREADS, 0, ps>>>(F, P, s0, nslots);
         launches += 2;
@@ -668,7 +689,7 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
         }
         // accumulate in pass order: the float additions per pixel follow the sample order of the reference's spp loop
         if (prev_acc) HJ_CUDA(c, cudaStreamWaitEvent(ps, prev_acc, 0));
-        k_accumulate<<<cdiv_u(WH, 256), 256, 0, ps>>>(F, P, c->aov_accum.as<float4>(), s0, nsamp, c->aov_path_rad.as<float4>(), c->aov_path_ids.as<uint2>());
+        k_accumulate<<<cdiv_u(F.npix, 256), 256, 0, ps>>>(F, P, c->aov_accum.as<float4>(), s0, nsamp, c->aov_path_rad.as<float4>(), c->aov_path_ids.as<uint2>());
         HJ_CUDA(c, cudaEventRecord(w.ev_acc, ps));
         prev_acc = w.ev_acc;
         launches++;

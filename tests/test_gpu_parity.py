@@ -181,3 +181,25 @@ def test_pinned_host_buffers_give_the_same_frame(gpu, cornell):
     assert np.array_equal(out.view(np.uint32), want.view(np.uint32))
     with pytest.raises(hj.HenjouError):
         gpu.unpin(out)                                       # not pinned any more
+
+
+@pytest.mark.parametrize("integrator", [abi.INTEGRATOR_MIS, abi.INTEGRATOR_PT])
+def test_pixel_band_passes_give_the_same_frame(gpu, cornell, integrator):
+    """Low-spp frames are cut into pixel bands so that every pipeline has a pass (option bands; auto for large frames
+    with fewer sample passes than pipelines). Slots are renumbered, RNG streams and the per-pixel sample order are not:
+    every AOV and every per-path record must be bit-identical to the unbanded frame."""
+    cornell.set_sky((0.8, 0.8, 0.8))
+    gpu.upload(cornell); gpu.build_accel()
+    fp = hj.frame_params(cornell, 75, 41, 3, frame=2, max_depth=6, integrator=integrator, debug_paths=1)   # 3075 px: ragged last band
+    out = {}
+    for bands in (1, 2, 7, 64):
+        gpu.set_option("bands", bands)
+        gpu.render(fp)
+        out[bands] = [gpu.readback(a).copy() for a in (abi.AOV_ACCUM, abi.AOV_COLOR, abi.AOV_ALBEDO, abi.AOV_NORMAL, abi.AOV_RGBA8,
+                                                       abi.AOV_PATH_RADIANCE, abi.AOV_PATH_IDS)]
+        assert gpu.stats()["passes"] >= bands - 1
+    gpu.set_option("bands", 0)
+    for bands in (2, 7, 64):
+        for a, b in zip(out[1], out[bands]):
+            assert np.array_equal(a.view(np.uint8), b.view(np.uint8)), bands
+    assert np.nansum(out[1][0][..., :3]) > 0

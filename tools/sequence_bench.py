@@ -3,7 +3,7 @@ read-back through the C ABI, against the fps.txt time budget of the reference's 
 the budget check it comments out at :1247-1254).  Compares the two per-frame update policies of hj_accel_build
 (full rebuild vs. refit of the first frame's topology) and finds the spp that fits the budget.
 
-    python tools/sequence_bench.py [frames=24] [fps=24] [spp=auto|N] [animated=24]  -> one JSON line
+    python tools/sequence_bench.py [frames=24] [fps=24] [spp=auto|N] [animated=24] [bands=N] [pipelines=N]  -> one JSON line
 """
 import json
 import os
@@ -25,6 +25,9 @@ budget_ms = 1000.0 / fps
 
 scene = scenes.rtcamp_like(animated=animated)
 r = hj.Renderer(0)
+for k in ("bands", "pipelines", "leaf_split", "builder"):      # kernel options for A/B runs
+    if k in opts:
+        r.set_option(k, int(opts[k]))
 r.upload(scene)
 rgba = np.empty((H, W, 4), np.uint8)
 r.pin(rgba)
