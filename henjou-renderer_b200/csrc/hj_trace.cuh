@@ -173,6 +173,15 @@ HJ_DI void fill_octant_perm(uint8_t (*perm)[256]) {
 #ifndef WAIT_MAX
 #define WAIT_MAX 4           // lanes waiting for their last triangle tests that force a partial batch
 #endif
+#ifndef HJ_STEAL
+#define HJ_STEAL 1           // intra-warp work stealing at the tail of the queue
+#endif
+#ifndef STEAL_ALWAYS
+#define STEAL_ALWAYS 0        // 1: also while the queue still has rays (lanes waiting for the next refill)
+#endif
+#ifndef STEAL_MIN_IDLE
+#define STEAL_MIN_IDLE 1     // idle lanes before a warp steals (r01-w sweep 1/16/24: 1 is best on C2, C3 and C5)
+#endif
 #ifndef TRI_K
 #define TRI_K 2              // a batch runs once pending pairs >= min(32, TRI_K x lanes doing node work)
 #endif
@@ -185,6 +194,7 @@ struct TraceShared {
     uint8_t perm[8][256];                           // octant permutation of the inner-child hit bits (fill_octant_perm)
     uint2 rring[HJ_TRACE_THREADS / 32][HJ_RCAP];    // pending leaf records: first triangle (leaf order), hit bits | owner lane << 24
     unsigned long long key0[HJ_TRACE_THREADS];      // QUERY 2: the emitter phase's result = the key the occlusion phase starts from
+    uint32_t helpers[HJ_TRACE_THREADS];             // lanes currently walking a stolen subtree of this thread's ray (HJ_STEAL)
 };
 
 // QUERY 0: closest hit. 1: any hit (occlusion). 2: "is the closest hit an emitter, and which" — the MIS emitter ray
@@ -211,6 +221,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
     uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u); int sp = 0;
     bool active = false, exhausted = false;
     bool emph = false;                              // QUERY 2: this lane is in its emitter phase
+    uint32_t own = tid;                             // thread whose ray this lane walks (itself unless it helps, HJ_STEAL)
     constexpr bool ANY = QUERY == 1;
     uint32_t nn0 = 0, own_tris = 0;
     const uint32_t k4b = load_two23();
@@ -219,7 +230,12 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
     while (true) {
         // ---- lanes whose walk is over and whose queued pairs are all tested hand their result over (once per burst,
         //      so that the write-out runs several lanes wide)
-        if (active && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u && (int32_t)(head - ticket) >= 0) {
+        if (active && own != tid && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u && (int32_t)(head - ticket) >= 0) {
+            atomicSub(&sh.helpers[own], 1u);        // a helper's part of its owner's ray is done (its triangle tests included)
+            active = false;
+        }
+        else if (active && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u && (int32_t)(head - ticket) >= 0 &&
+                 (!HJ_STEAL || *(volatile uint32_t*)&sh.helpers[tid] == 0u)) {
             const unsigned long long k = sh.key[tid];
             if (QUERY == 2 && emph) {               // emitter phase over: walk again from the root for anything in front of it
                 emph = false; sh.key0[tid] = k;
@@ -253,11 +269,46 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                     sh.bary[tid] = make_float2(0.0f, 0.0f);
                     ng = make_uint2(0u, 0x80000000u);     // the root, as the only inner hit of a virtual parent
                     tg = make_uint2(0u, 0u); sp = 0; ticket = head;
-                    active = true; nn0 = n_nodes; own_tris = 0; emph = QUERY == 2;
+                    active = true; nn0 = n_nodes; own_tris = 0; emph = QUERY == 2; own = tid; sh.helpers[tid] = 0u;
                 }
             }
             if (base + (uint32_t)__popc(idle) >= n) exhausted = true;
         }
+#if HJ_STEAL
+        // ---- tail of the queue: idle lanes take over pending subtrees of the lanes that are still walking. The closest hit
+        //      is a minimum over triangles (atomicMin on the owner's key), so it does not matter which lane walks which
+        //      subtree: a helper walks with the owner's ray, prunes with the owner's current best and queues leaf records in
+        //      the owner's name. One helper per victim and round; helpers can be robbed in turn. The longest rays
+        //      (thousands of node visits against a mean of 15) otherwise keep a warp at 1 of 32 lanes for milliseconds.
+        if (exhausted || STEAL_ALWAYS) {
+            const uint32_t idle2 = __ballot_sync(FULL, !active);
+            const uint32_t vict = __ballot_sync(FULL, active && sp > 0);
+            if (__popc(idle2) >= STEAL_MIN_IDLE && vict) {
+                const uint32_t npair = min(__popc(idle2), __popc(vict));
+                const uint32_t irank = __popc(idle2 & ((1u << lane) - 1u)), vrank = __popc(vict & ((1u << lane) - 1u));
+                const bool thief = !active && irank < npair, robbed = active && sp > 0 && vrank < npair;
+                const uint32_t src = thief ? __fns(vict, 0, (int)irank + 1) : lane;
+                const float sox = __shfl_sync(FULL, o.x, src), soy = __shfl_sync(FULL, o.y, src), soz = __shfl_sync(FULL, o.z, src);
+                const float six = __shfl_sync(FULL, idir.x, src), siy = __shfl_sync(FULL, idir.y, src), siz = __shfl_sync(FULL, idir.z, src);
+                const uint32_t soct = __shfl_sync(FULL, oct, src), sown = __shfl_sync(FULL, own, src);
+                const float stmin = __shfl_sync(FULL, tmin, src);
+                const uint32_t semph = __shfl_sync(FULL, (uint32_t)emph, src);
+                uint2 loot = make_uint2(0u, 0u);
+                if (thief) loot = sh.stack[wbase + src];                    // the victim's oldest entry: the largest pending subtrees
+                __syncwarp();
+                if (robbed) {                                               // the newest entry takes its place
+                    sp--;
+                    if (sp > 0) sstack[0] = sp < HJ_SSTACK ? sstack[sp * HJ_TRACE_THREADS] : l_stack[sp - HJ_SSTACK];
+                }
+                if (thief) {
+                    o = f3(sox, soy, soz); idir = f3(six, siy, siz); oct = soct; tmin = stmin; emph = semph != 0u; own = sown;
+                    ng = loot; tg = make_uint2(0u, 0u); sp = 0; ticket = head; active = true; nn0 = n_nodes; own_tris = 0;
+                    atomicAdd(&sh.helpers[own], 1u);
+                }
+                __syncwarp();
+            }
+        }
+#endif
         if (!__any_sync(FULL, active)) { if (exhausted) break; else continue; }
 #pragma unroll 1
         for (int it = 0; it < TRACE_BURST; it++) {
@@ -272,7 +323,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                     const uint32_t node = ng.x + __popc(ng.y & 0xffu & ((1u << slot) - 1u));
                     if (ng.y > 0x00ffffffu) { if (sp < HJ_SSTACK) sstack[sp * HJ_TRACE_THREADS] = ng; else l_stack[sp - HJ_SSTACK] = ng; sp++; }
                     if (COUNT) n_nodes++;
-                    const float tcur = __uint_as_float((uint32_t)(sh.key[tid] >> 32));
+                    const float tcur = __uint_as_float((uint32_t)(sh.key[own] >> 32));
                     node_boxes<QUERY == 2>(S.nodes, node, o, idir, oct, tmin, tcur, k4b, sh.perm[oct ^ 7u], emph, ng, tg);
                     did = true;
                 }
@@ -284,7 +335,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
             if (has) {
                 if (cnt != 0u) {
                     const uint32_t pos = tail + (uint32_t)__popc(has & ((1u << lane) - 1u));
-                    rring[pos & (HJ_RCAP - 1)] = make_uint2(tg.x, tg.y | (lane << 24));
+                    rring[pos & (HJ_RCAP - 1)] = make_uint2(tg.x, tg.y | ((own & 31u) << 24));
                     tg.y = 0u; ticket = pos + 1u; if (COUNT) own_tris += cnt;
                 }
                 tail += (uint32_t)__popc(has);
@@ -356,8 +407,8 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                 thr = 32u;                                         // after a forced partial batch only full ones
             }
             // ---- any hit ends an occlusion ray
-            if (ANY && active && (uint32_t)sh.key[tid] != 0xffffffffu) { ng.y = 0u; tg.y = 0u; sp = 0; }
-            if (QUERY == 2 && active && !emph && sh.key[tid] != sh.key0[tid]) { ng.y = 0u; tg.y = 0u; sp = 0; }
+            if (ANY && active && (uint32_t)sh.key[own] != 0xffffffffu) { ng.y = 0u; tg.y = 0u; sp = 0; }
+            if (QUERY == 2 && active && !emph && sh.key[own] != sh.key0[own]) { ng.y = 0u; tg.y = 0u; sp = 0; }
         }
     }
     if (COUNT && diag && lane == 0) {
