@@ -165,7 +165,13 @@ int hj_create(hj_ctx** out, int device);
 void hj_destroy(hj_ctx* ctx);
 const char* hj_last_error(const hj_ctx* ctx);   /* ctx may be NULL: last hj_create error */
 
-/* "count_fetches" 0|1, "time_stages" 0|1, "paths_per_pass" N (0 = auto), "leaf_max" 1..3 (triangles per BVH leaf) */
+/* Tuning / diagnostic options (none changes a result):
+ *   "count_fetches" 0|1, "time_stages" 0|1       counters pass / serial event-pair timing of the stages (hj_stats)
+ *   "paths_per_pass" N (0 = auto), "pipelines" 1..8, "bands" 0 (auto)..64 (pixel bands of a low-spp frame)
+ *   "builder" 0 LBVH | 1 PLOC (default), "leaf_max" 1..3 (triangles per BVH leaf), "leaf_split" 0|1 (default 1: free
+ *   slots of a wide node split multi-triangle leaves), "mis_emitter_first" 0|1, "trace_blocks_per_sm" 0 (auto)..32
+ *   "verify_accel" 0|1 (also env HJ_VERIFY_ACCEL=1): every hj_accel_build checks the BVH it built (each leaf triangle
+ *   inside its slot's box, every primitive in exactly one leaf) and fails with HJ_ERR_INVALID otherwise */
 int hj_set_option(hj_ctx* ctx, const char* key, int64_t value);
 
 /* ≙ Renderer::cpySceneDataToDevice + textureBind + setSky + setLUT (renderer.h:197-255, 740-898). */
