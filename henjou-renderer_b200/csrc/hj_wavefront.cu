@@ -317,18 +317,19 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S
 
 HJ_DI void finish_extend(const FrameK& F, const WfPtrs& P, uint32_t slot, const Hit& h) {
     P.hit[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.prim));
-    float4 L = P.L[slot];
-    if (F.debug) {
+    if (F.debug) {                         // L.w = rays traced by this path: only the debug records read it
+        float4 L = P.L[slot];
         uint2 g = P.dbg[slot];
         if (L.w == 0.0f) g.x = h.prim;     // first ray of the path
         g.y = (g.y ^ (h.prim + 1u)) * 0x01000193u;
         P.dbg[slot] = g;
+        L.w += 1.0f;
+        P.L[slot] = L;
     }
-    L.w += 1.0f;
-    P.L[slot] = L;
 }
 // TraceOcculution (rt.h:15-41): any hit in (1e-3, dist-1e-3) discards the light sample
-HJ_DI void finish_shadow(const WfPtrs& P, uint32_t slot, const Hit& h) {
+HJ_DI void finish_shadow(const FrameK& F, const WfPtrs& P, uint32_t slot, const Hit& h) {
+    if (h.prim != 0xffffffffu && !F.debug) return;         // occluded: nothing to add (the ray count is a debug record)
     float4 L = P.L[slot];
     if (h.prim == 0xffffffffu) { const float4 c = P.sh_c[slot]; L.x += c.x; L.y += c.y; L.z += c.z; }
     L.w += 1.0f;
@@ -336,6 +337,7 @@ HJ_DI void finish_shadow(const WfPtrs& P, uint32_t slot, const Hit& h) {
 }
 // the extra BSDF-sampled ray of MIS (rt.h:383-420): emitter hit weighted by the balance heuristic, sky unweighted
 HJ_DI void finish_mis(const DevScene& S, const FrameK& F, const WfPtrs& P, uint32_t slot, const Hit& h) {
+    if (h.prim == HJ_HIT_BLOCKED && !F.debug) return;      // blocked by a non-emitter: no contribution, nothing to load
     const float4 oq = P.mi_o[slot], dq = P.mi_d[slot], aq = P.mi_a[slot];
     const float3 org = f3(oq), wi = f3(dq), f = f3(aq), thr = f3(P.mi_t[slot]);
     const float c1 = oq.w, ppdf = dq.w;
@@ -384,7 +386,7 @@ struct WfRayIO {
     }
     HJ_DI void finish(const Hit& h) {
         if (MODE == 0) finish_extend(F, P, slot, h);
-        else if (MODE == 1) finish_shadow(P, slot, h);
+        else if (MODE == 1) finish_shadow(F, P, slot, h);
         else finish_mis(S, F, P, slot, h);
     }
 };
