@@ -24,8 +24,15 @@
 #include "hj_scene.cuh"
 
 #define HJ_STACK 96          // local-memory part of the traversal stack
+// Shared-memory part of the stack (entries per thread). What the 8 resident blocks do not take stays L1, in steps of the
+// carve-out sizes: 8 x (block + 1 KB reserved) <= 132 KB leaves 124 KB of L1 instead of 92 KB. r01-w: 8 entries (20 KB
+// per block, 164 KB carve-out) -> 3 entries: C2 -1.0 %, C5 -1.5 %; 2 entries lose it again to local-memory traffic. The
+// queries without the key0 array have room for a fourth entry under the same limit.
+#ifndef HJ_SSTACK_Q2
+#define HJ_SSTACK_Q2 3
+#endif
 #ifndef HJ_SSTACK
-#define HJ_SSTACK 8          // shared-memory part (entries per thread); what the blocks do not take stays L1 (ss12 -> ss8: +2 %)
+#define HJ_SSTACK 4
 #endif
 #define HJ_TRACE_THREADS 128 // block size of every kernel that traverses
 #define HJ_NODE_QUADS 7      // 16-byte words per node (112 B)
@@ -186,14 +193,16 @@ HJ_DI void fill_octant_perm(uint8_t (*perm)[256]) {
 #define TRI_K 2              // a batch runs once pending pairs >= min(32, TRI_K x lanes doing node work)
 #endif
 
+template <int QUERY>
 struct TraceShared {
-    uint2 stack[(HJ_SSTACK ? HJ_SSTACK : 1) * HJ_TRACE_THREADS];
+    static constexpr int SS = QUERY == 2 ? HJ_SSTACK_Q2 : HJ_SSTACK;
+    uint2 stack[(SS ? SS : 1) * HJ_TRACE_THREADS];
     uint32_t ray[9][HJ_TRACE_THREADS];              // ox oy oz Sx Sy Sz (kx | ky<<2 | kz<<4) tmin tmax
     unsigned long long key[HJ_TRACE_THREADS];       // best hit: t bits << 32 | prim (miss: tmax bits << 32 | 0xffffffff)
     float2 bary[HJ_TRACE_THREADS];                  // barycentrics of the best hit
     uint8_t perm[8][256];                           // octant permutation of the inner-child hit bits (fill_octant_perm)
     uint2 rring[HJ_TRACE_THREADS / 32][HJ_RCAP];    // pending leaf records: first triangle (leaf order), hit bits | owner lane << 24
-    unsigned long long key0[HJ_TRACE_THREADS];      // QUERY 2: the emitter phase's result = the key the occlusion phase starts from
+    unsigned long long key0[QUERY == 2 ? HJ_TRACE_THREADS : 1];   // QUERY 2: the emitter phase's result = the key the occlusion phase starts from
     uint32_t helpers[HJ_TRACE_THREADS];             // lanes currently walking a stolen subtree of this thread's ray (HJ_STEAL)
 };
 
@@ -207,10 +216,11 @@ struct TraceShared {
 
 // IO: uint32_t count; bool load(idx, o, d, tmin, tmax) (false: empty entry); void finish(const Hit&)
 template <int QUERY, bool COUNT, class IO>
-HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next, TraceShared& sh, uint2* l_stack,
+HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next, TraceShared<QUERY>& sh, uint2* l_stack,
                            uint32_t& n_rays, uint32_t& n_nodes, uint32_t& n_tris, uint32_t* max_nodes, uint32_t* max_tris,
                            unsigned long long* diag = nullptr) {
     const uint32_t FULL = 0xffffffffu;
+    constexpr int SS = TraceShared<QUERY>::SS;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, wbase = tid & ~31u;
     uint2* rring = sh.rring[tid >> 5];
     uint32_t npairs = 0;                            // warp-uniform: triangle tests pending in the ring
@@ -298,7 +308,7 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
                 __syncwarp();
                 if (robbed) {                                               // the newest entry takes its place
                     sp--;
-                    if (sp > 0) sstack[0] = sp < HJ_SSTACK ? sstack[sp * HJ_TRACE_THREADS] : l_stack[sp - HJ_SSTACK];
+                    if (sp > 0) sstack[0] = sp < SS ? sstack[sp * HJ_TRACE_THREADS] : l_stack[sp - SS];
                 }
                 if (thief) {
                     o = f3(sox, soy, soz); idir = f3(six, siy, siz); oct = soct; tmin = stmin; emph = semph != 0u; own = sown;
@@ -315,13 +325,13 @@ HJ_DI void trace_warp_loop(const DevScene& S, IO& io, uint32_t n, uint32_t* next
             // ---- node phase: every lane without un-queued triangles visits its nearest pending inner child
             bool did = false;
             if (active && tg.y == 0u) {
-                if (ng.y <= 0x00ffffffu && sp > 0) { sp--; ng = sp < HJ_SSTACK ? sstack[sp * HJ_TRACE_THREADS] : l_stack[sp - HJ_SSTACK]; }
+                if (ng.y <= 0x00ffffffu && sp > 0) { sp--; ng = sp < SS ? sstack[sp * HJ_TRACE_THREADS] : l_stack[sp - SS]; }
                 if (ng.y > 0x00ffffffu) {
                     const uint32_t k = 31u - (uint32_t)__clz(ng.y);      // highest bit = nearest (slots permuted by the octant)
                     ng.y &= ~(1u << k);
                     const uint32_t slot = (k - 24u) ^ (oct ^ 7u);
                     const uint32_t node = ng.x + __popc(ng.y & 0xffu & ((1u << slot) - 1u));
-                    if (ng.y > 0x00ffffffu) { if (sp < HJ_SSTACK) sstack[sp * HJ_TRACE_THREADS] = ng; else l_stack[sp - HJ_SSTACK] = ng; sp++; }
+                    if (ng.y > 0x00ffffffu) { if (sp < SS) sstack[sp * HJ_TRACE_THREADS] = ng; else l_stack[sp - SS] = ng; sp++; }
                     if (COUNT) n_nodes++;
                     const float tcur = __uint_as_float((uint32_t)(sh.key[own] >> 32));
                     node_boxes<QUERY == 2>(S.nodes, node, o, idir, oct, tmin, tcur, k4b, sh.perm[oct ^ 7u], emph, ng, tg);

@@ -393,12 +393,12 @@ struct WfRayIO {
 
 template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace(DevScene S, FrameK F, WfPtrs P, int cur) {
-    __shared__ TraceShared sh;
+    constexpr int QUERY = MODE == 1 ? 1 : (MODE == 3 ? 2 : 0), CTR = MODE == 3 ? 2 : MODE;
+    __shared__ TraceShared<QUERY> sh;
     uint2 l_stack[HJ_STACK];
     const uint32_t n = MODE == 0 ? P.cnt->n_extend[cur] : (MODE == 1 ? P.cnt->n_shadow : P.cnt->n_mis);
     WfRayIO<MODE> io{S, F, P, MODE == 0 ? P.q_ext[cur] : (MODE == 1 ? P.q_shadow : P.q_mis), 0u};
     uint32_t nr = 0, nn = 0, nt = 0;
-    constexpr int QUERY = MODE == 1 ? 1 : (MODE == 3 ? 2 : 0), CTR = MODE == 3 ? 2 : MODE;
     trace_warp_loop<QUERY, COUNT>(S, io, n, &P.cnt->next[CTR], sh, l_stack, nr, nn, nt, &P.cnt->max_nodes, &P.cnt->max_tris, P.cnt->diag[CTR]);
     warp_add64(MODE == 1 ? &P.cnt->rays_shadow : &P.cnt->rays_extend, nr);
     if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
@@ -470,7 +470,7 @@ struct BatchRayIO {
 };
 template <bool ANY>
 __global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace_batch(DevScene S, const float4* rays, uint32_t n, uint32_t* prim, float* tuv, uint32_t* cursor) {
-    __shared__ TraceShared sh;
+    __shared__ TraceShared<ANY ? 1 : 0> sh;
     uint2 l_stack[HJ_STACK];
     BatchRayIO<ANY> io{rays, prim, tuv, 0u};
     uint32_t nr = 0, nn = 0, nt = 0;
