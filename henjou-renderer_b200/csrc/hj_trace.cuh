@@ -25,9 +25,9 @@
 
 #define HJ_STACK 96          // local-memory part of the traversal stack
 // Shared-memory part of the stack (entries per thread). What the 8 resident blocks do not take stays L1, in steps of the
-// carve-out sizes: 8 x (block + 1 KB reserved) <= 132 KB leaves 124 KB of L1 instead of 92 KB. r01-w: 8 entries (20 KB
-// per block, 164 KB carve-out) -> 3 entries: C2 -1.0 %, C5 -1.5 %; 2 entries lose it again to local-memory traffic. The
-// queries without the key0 array have room for a fourth entry under the same limit.
+// carve-out (ncu launch__shared_mem_config_size): the 20.5 KB layout of r01-v (8 entries) got 196 KiB, i.e. 60 KB of L1;
+// 8 x (15.4 KB + 1 KB reserved) = 131 KB fits the 132 KiB step and leaves 124 KB: L1 hit 51 -> 63 %, C2 -1.2 %, C5 -0.9 %.
+// 2 entries lose it again to local-memory traffic. The queries without the key0 array have room for a fourth entry.
 #ifndef HJ_SSTACK_Q2
 #define HJ_SSTACK_Q2 3
 #endif
