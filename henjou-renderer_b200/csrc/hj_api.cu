@@ -21,6 +21,15 @@ static int upload(hj_ctx* c, DevBuf& b, const T* src, size_t n) {
     return HJ_OK;
 }
 
+// tri_inst[t] = the instance whose [prim_offsets[i], prim_offsets[i+1]) contains triangle t (prim_offsets strictly increasing)
+__global__ void k_tri_inst(const uint32_t* __restrict__ prim_offsets, uint32_t n_inst, uint32_t n_tris, uint32_t* __restrict__ tri_inst) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tris) return;
+    uint32_t lo = 0, hi = n_inst;                 // last i with prim_offsets[i] <= t
+    while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (prim_offsets[mid] <= t) lo = mid; else hi = mid; }
+    tri_inst[t] = lo;
+}
+
 extern "C" {
 
 int hj_abi_version(void) { return HJ_ABI_VERSION; }
@@ -119,10 +128,6 @@ int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
     HJ_REQUIRE(c, d->prim_offsets[0] == 0, HJ_ERR_INVALID, "hj_scene_upload: prim_offsets[0] must be 0");
     for (uint32_t i = 1; i < d->n_instances; i++)
         HJ_REQUIRE(c, d->prim_offsets[i] > d->prim_offsets[i - 1] && d->prim_offsets[i] < d->n_triangles, HJ_ERR_INVALID, "hj_scene_upload: prim_offsets must be strictly increasing and < n_triangles");
-    for (size_t i = 0; i < 3 * (size_t)d->n_triangles; i++)
-        HJ_REQUIRE(c, d->indices[i] < d->n_vertices, HJ_ERR_INVALID, "hj_scene_upload: vertex index out of range");
-    for (uint32_t i = 0; i < d->n_triangles; i++)
-        HJ_REQUIRE(c, d->material_ids[i] < d->n_materials, HJ_ERR_INVALID, "hj_scene_upload: material id out of range");
     for (uint32_t i = 0; i < d->n_light_prims; i++)
         HJ_REQUIRE(c, d->light_prim_ids && d->light_prim_emission && d->light_prim_ids[i] < d->n_triangles, HJ_ERR_INVALID, "hj_scene_upload: bad light primitive list");
     HJ_CUDA(c, cudaSetDevice(c->device));
@@ -135,20 +140,30 @@ int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
         std::vector<float> tmp;
         if (!d->normals) { tmp.assign(3 * nv, 0.0f); for (size_t i = 0; i < nv; i++) tmp[3 * i + 1] = 1.0f; }
         if ((rc = upload(c, c->d_normals, d->normals ? d->normals : tmp.data(), 3 * nv))) return rc;
-        HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (!d->normals) HJ_CUDA(c, cudaStreamSynchronize(c->stream));          // tmp is reused / freed below
         if (!d->texcoords) tmp.assign(2 * nv, 0.0f);
         if ((rc = upload(c, c->d_texcoords, d->texcoords ? d->texcoords : tmp.data(), 2 * nv))) return rc;
-        HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (!d->texcoords) HJ_CUDA(c, cudaStreamSynchronize(c->stream));
     }
     if ((rc = upload(c, c->d_indices, d->indices, 3 * nt))) return rc;
     if ((rc = upload(c, c->d_material_ids, d->material_ids, nt))) return rc;
     if ((rc = upload(c, c->d_prim_offsets, d->prim_offsets, (size_t)d->n_instances))) return rc;
-    std::vector<uint32_t> tri_inst(nt);
-    for (uint32_t i = 0; i < d->n_instances; i++) {
-        const uint32_t b = d->prim_offsets[i], e = (i + 1 < d->n_instances) ? d->prim_offsets[i + 1] : d->n_triangles;
-        for (uint32_t t = b; t < e; t++) tri_inst[t] = i;
+    // owning instance per triangle: derived on the device from prim_offsets (no host pass, no extra upload)
+    HJ_CUDA(c, c->d_tri_inst.reserve(nt * sizeof(uint32_t)));
+    k_tri_inst<<<(uint32_t)((nt + 255) / 256), 256, 0, c->stream>>>(c->d_prim_offsets.as<uint32_t>(), d->n_instances, d->n_triangles, c->d_tri_inst.as<uint32_t>());
+    // range checks of the two big index arrays run on the host while the copies above are in flight (they come out of
+    // page-locked memory when the caller used hj_host_pin); a violation leaves the context without a scene
+    {
+        uint32_t max_index = 0, max_material = 0;
+        const uint32_t* idx = d->indices; const size_t ni = 3 * nt;
+        for (size_t i = 0; i < ni; i++) max_index = idx[i] > max_index ? idx[i] : max_index;
+        for (size_t i = 0; i < nt; i++) max_material = d->material_ids[i] > max_material ? d->material_ids[i] : max_material;
+        if (max_index >= d->n_vertices || max_material >= d->n_materials) {
+            cudaStreamSynchronize(c->stream);
+            c->err = max_index >= d->n_vertices ? "hj_scene_upload: vertex index out of range" : "hj_scene_upload: material id out of range";
+            return HJ_ERR_INVALID;
+        }
     }
-    if ((rc = upload(c, c->d_tri_inst, tri_inst.data(), nt))) return rc;
     std::vector<DevMaterial> mats(d->n_materials);
     for (uint32_t i = 0; i < d->n_materials; i++) {
         const hj_material& m = d->materials[i]; DevMaterial& o = mats[i];

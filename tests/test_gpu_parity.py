@@ -162,6 +162,19 @@ def test_error_paths(gpu, cornell):
     bad = hj.frame_params(cornell, 0, 8, 1)
     with pytest.raises(hj.HenjouError):
         r.render(bad)
+    # a vertex index / material id out of range is refused (checked on the host while the copies are in flight) and
+    # leaves the context without a scene; a good upload afterwards works again
+    import copy
+    for field, value in (("indices", cornell.vertices.shape[0]), ("material_ids", len(cornell.materials))):
+        broken = copy.copy(cornell)
+        arr = getattr(cornell, field).copy(); arr[-1] = value
+        setattr(broken, field, arr)
+        with pytest.raises(hj.HenjouError, match="out of range"):
+            r.upload(broken)
+        with pytest.raises(hj.HenjouError):
+            r.build_accel()
+    r.upload(cornell); r.build_accel(); r.render(hj.frame_params(cornell, 8, 8, 1))
+    assert np.isfinite(r.readback(abi.AOV_COLOR)).all()
     r.close()
 
 
