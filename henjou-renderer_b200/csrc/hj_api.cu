@@ -104,6 +104,7 @@ int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
     else if (!strcmp(key, "leaf_max")) { HJ_REQUIRE(c, value >= 1 && value <= 3, HJ_ERR_INVALID, "hj_set_option: leaf_max must be 1..3"); c->opt_leaf_max = (int)value; }
     else if (!strcmp(key, "leaf_split")) c->opt_leaf_split = value != 0;
     else if (!strcmp(key, "bands")) { HJ_REQUIRE(c, value >= 0 && value <= 64, HJ_ERR_INVALID, "hj_set_option: bands must be 0 (auto) .. 64"); c->opt_bands = (int)value; }
+    else if (!strcmp(key, "ploc_tail")) { c->opt_ploc_tail = value != 0; c->bvh.have_topology = false; }
     else if (!strcmp(key, "verify_accel")) c->opt_verify_accel = value != 0;
     else if (!strcmp(key, "mis_emitter_first")) c->opt_mis_emitter_first = value != 0;
     else if (!strcmp(key, "denoise_iterations")) { HJ_REQUIRE(c, value >= 0 && value <= 8, HJ_ERR_INVALID, "hj_set_option: denoise_iterations must be 0..8"); c->opt_denoise_iterations = (int)value; }

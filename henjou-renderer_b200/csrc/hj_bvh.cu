@@ -324,6 +324,74 @@ __global__ void __launch_bounds__(PLOC_THREADS) k_ploc_compact(int n, const uint
     }
 }
 
+// The last rounds of PLOC work on a handful of clusters and are pure launch + host-synchronisation latency (C2: 67 rounds,
+// ~50 of them on fewer than 1024 clusters, ~45 us each). Once the clusters fit one block, this kernel runs the remaining
+// rounds in shared memory: the same nearest-neighbour rule, merges and compaction as k_ploc_nn / k_ploc_merge /
+// k_ploc_compact, so the tree is the same.
+#define PLOC_TAIL 1024
+__global__ void __launch_bounds__(PLOC_TAIL) k_ploc_tail(int n, int n_leaves, const uint32_t* __restrict__ cid_in, const float4* __restrict__ clo_in,
+                                                          const float4* __restrict__ chi_in, uint32_t* node_ctr, uint32_t* left, uint32_t* right, uint32_t* parent,
+                                                          uint32_t* cnt, float4* blo, float4* bhi) {
+    __shared__ float4 s_lo[PLOC_TAIL], s_hi[PLOC_TAIL];
+    __shared__ uint32_t s_cid[PLOC_TAIL];
+    __shared__ int s_nn[PLOC_TAIL];
+    __shared__ uint32_t s_wsum[PLOC_TAIL / 32];
+    const int i = threadIdx.x, w = i >> 5, lane = i & 31;
+    if (i < n) { s_cid[i] = cid_in[i]; s_lo[i] = clo_in[i]; s_hi[i] = chi_in[i]; }
+    __syncthreads();
+    int cur = n;
+    while (cur > 1) {
+        if (i < cur) {                                   // k_ploc_nn
+            const float4 lo = s_lo[i], hi = s_hi[i];
+            float best = FLT_MAX; int bj = -1;
+            const int j0 = max(0, i - PLOC_RADIUS), j1 = min(cur - 1, i + PLOC_RADIUS);
+            for (int j = j0; j <= j1; j++) {
+                if (j == i) continue;
+                const float d = merged_area(lo, hi, s_lo[j], s_hi[j]);
+                bool better = d < best;
+                if (d == best && bj >= 0) {
+                    const int a0 = min(i, j), a1 = max(i, j), b0 = min(i, bj), b1 = max(i, bj);
+                    better = a0 < b0 || (a0 == b0 && a1 < b1);
+                }
+                if (better) { best = d; bj = j; }
+            }
+            s_nn[i] = bj;
+        }
+        __syncthreads();
+        bool keep = false;                               // k_ploc_merge
+        uint32_t my_cid = 0; float4 my_lo = make_float4(0, 0, 0, 0), my_hi = my_lo;
+        if (i < cur) {
+            const int j = s_nn[i];
+            const bool mutual = j >= 0 && s_nn[j] == i;
+            keep = true; my_cid = s_cid[i]; my_lo = s_lo[i]; my_hi = s_hi[i];
+            if (mutual) {
+                if (i < j) {
+                    const uint32_t id = atomicAdd(node_ctr, 1u);
+                    const uint32_t a = my_cid, b = s_cid[j];
+                    const float4 xlo = s_lo[j], xhi = s_hi[j];
+                    const float4 lo = make_float4(fminf(my_lo.x, xlo.x), fminf(my_lo.y, xlo.y), fminf(my_lo.z, xlo.z), fmaxf(my_lo.w, xlo.w));
+                    const float4 hi = make_float4(fmaxf(my_hi.x, xhi.x), fmaxf(my_hi.y, xhi.y), fmaxf(my_hi.z, xhi.z), 0.0f);
+                    left[id] = a; right[id] = b; parent[a] = id; parent[b] = id;
+                    cnt[id] = (a >= (uint32_t)(n_leaves - 1) ? 1u : cnt[a]) + (b >= (uint32_t)(n_leaves - 1) ? 1u : cnt[b]);
+                    blo[id] = lo; bhi[id] = hi;
+                    my_cid = id; my_lo = lo; my_hi = hi;
+                } else keep = false;
+            }
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, keep);      // k_ploc_compact (stable)
+        if (lane == 0) s_wsum[w] = (uint32_t)__popc(m);
+        __syncthreads();                                 // also: every read of s_* of this round is done
+        uint32_t base = 0, total = 0;
+        for (int ww = 0; ww < PLOC_TAIL / 32; ww++) { const uint32_t v = s_wsum[ww]; if (ww < w) base += v; total += v; }
+        if (keep) {
+            const uint32_t pos = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+            s_cid[pos] = my_cid; s_lo[pos] = my_lo; s_hi[pos] = my_hi;
+        }
+        __syncthreads();
+        cur = (int)total;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------- collapse to 8-wide
 struct CollapseArgs {
     int n; uint32_t leaf_max; int leaf_split;
@@ -615,6 +683,11 @@ int hj_bvh_build(hj_ctx* c, int mode) {
                                                       B.blo.as<float4>(), B.bhi.as<float4>());
             uint32_t cur_n = n; int pp = 0, rounds = 0;
             while (cur_n > 1) {
+                if (cur_n <= PLOC_TAIL && c->opt_ploc_tail) {            // the remaining rounds in one block, no host round trips
+                    k_ploc_tail<<<1, PLOC_TAIL, 0, st>>>((int)cur_n, (int)n, B.p_cid[pp].as<uint32_t>(), B.p_lo[pp].as<float4>(), B.p_hi[pp].as<float4>(), B.counters.as<uint32_t>(),
+                                                         B.left.as<uint32_t>(), B.right.as<uint32_t>(), B.parent.as<uint32_t>(), B.cnt.as<uint32_t>(), B.blo.as<float4>(), B.bhi.as<float4>());
+                    break;
+                }
                 const uint32_t nb = cdiv(cur_n, PLOC_THREADS);
                 k_ploc_nn<<<nb, PLOC_THREADS, 0, st>>>((int)cur_n, B.p_lo[pp].as<float4>(), B.p_hi[pp].as<float4>(), B.p_nn.as<uint32_t>());
                 k_ploc_merge<<<nb, PLOC_THREADS, 0, st>>>((int)cur_n, (int)n, B.p_cid[pp].as<uint32_t>(), B.p_lo[pp].as<float4>(), B.p_hi[pp].as<float4>(), B.p_nn.as<uint32_t>(),

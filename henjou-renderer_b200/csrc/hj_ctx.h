@@ -64,7 +64,7 @@ struct hj_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err;
     // options
-    int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3, opt_trace_blocks_per_sm = 0, opt_pipelines = 8, opt_builder = 1, opt_mis_emitter_first = 1, opt_leaf_split = 1, opt_verify_accel = 0, opt_bands = 0;   // builder: 0 Karras radix tree (LBVH), 1 PLOC
+    int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3, opt_trace_blocks_per_sm = 0, opt_pipelines = 8, opt_builder = 1, opt_mis_emitter_first = 1, opt_leaf_split = 1, opt_verify_accel = 0, opt_bands = 0, opt_ploc_tail = 1;   // builder: 0 Karras radix tree (LBVH), 1 PLOC
     int64_t opt_paths_per_pass = 0;
     // scene
     bool have_scene = false, have_accel = false, have_frame = false;

@@ -168,7 +168,7 @@ const char* hj_last_error(const hj_ctx* ctx);   /* ctx may be NULL: last hj_crea
 /* Tuning / diagnostic options (none changes a result):
  *   "count_fetches" 0|1, "time_stages" 0|1       counters pass / serial event-pair timing of the stages (hj_stats)
  *   "paths_per_pass" N (0 = auto), "pipelines" 1..8, "bands" 0 (auto)..64 (pixel bands of a low-spp frame)
- *   "builder" 0 LBVH | 1 PLOC (default), "leaf_max" 1..3 (triangles per BVH leaf), "leaf_split" 0|1 (default 1: free
+ *   "builder" 0 LBVH | 1 PLOC (default), "ploc_tail" 0|1 (last PLOC rounds in one block), "leaf_max" 1..3 (triangles per BVH leaf), "leaf_split" 0|1 (default 1: free
  *   slots of a wide node split multi-triangle leaves), "mis_emitter_first" 0|1, "trace_blocks_per_sm" 0 (auto)..32
  *   "verify_accel" 0|1 (also env HJ_VERIFY_ACCEL=1): every hj_accel_build checks the BVH it built (each leaf triangle
  *   inside its slot's box, every primitive in exactly one leaf) and fails with HJ_ERR_INVALID otherwise */

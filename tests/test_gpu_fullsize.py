@@ -68,7 +68,7 @@ def test_c2_full_frame_does_not_depend_on_tree_or_pass_layout(gpu, c2):
         got, _ = _frame(gpu, fp)
         gpu.set_option(key, back)
         assert _same(ref, got), (key, val)
-    for key, val, back in (("leaf_split", 0, 1), ("builder", 0, 1), ("leaf_max", 1, 3)):
+    for key, val, back in (("leaf_split", 0, 1), ("builder", 0, 1), ("leaf_max", 1, 3), ("ploc_tail", 0, 1)):
         gpu.set_option(key, val); gpu.build_accel(xf, inv)
         got, _ = _frame(gpu, fp)
         gpu.set_option(key, back)

@@ -111,6 +111,11 @@ def test_c5_many_triangles_and_builders(gpu):
         p, t = gpu.trace(rays[:20000])
         assert np.array_equal(p, p0[:20000]) and np.array_equal(t, t0[:20000])
         gpu.set_option("leaf_split", 1)
+        # PLOC with every round as separate launches (no single-block tail): same tree, same answers
+        gpu.set_option("ploc_tail", 0); gpu.build_accel()
+        p, t = gpu.trace(rays[:20000])
+        assert np.array_equal(p, p0[:20000]) and np.array_equal(t, t0[:20000])
+        gpu.set_option("ploc_tail", 1)
     gpu.set_option("builder", 0)
     assert (p0 != 0xffffffff).mean() > 0.5
 
