@@ -67,8 +67,11 @@ if opts.get("spp", "auto") == "auto":
     probe = summary(run_sequence(2, "refit"))
     per_spp = max(probe["render_ms_mean"] / 2.0, 1e-3)
     spp = max(1, int((budget_ms - probe["accel_ms_mean"] - 2.0) / per_spp))
-    while spp > 1 and summary(run_sequence(spp, "refit"))["frames_over_budget"]:
+    fits = lambda n: summary(run_sequence(n, "refit"))["frames_over_budget"] == 0
+    while spp > 1 and not fits(spp):
         spp -= 1
+    while spp < 64 and fits(spp + 1):                    # the 2-spp probe overestimates the cost per sample: try upwards too
+        spp += 1
 else:
     spp = int(opts["spp"])
 
