@@ -111,14 +111,15 @@ def cpu_arm(scene, cfg, budget_s=15.0, steps=1, warmup=0):
     xf, inv = scene.transforms(cfg["frame"] / 24.0)
     o = ob.Oracle(scene, kind, xforms=xf, inv_xforms=inv)
     W, H = cfg["width"], cfg["height"]
-    cores = os.cpu_count() or 1
+    # explicit thread count: torchrun exports OMP_NUM_THREADS=1, which would leave the CPU arm on one core at N > 1
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     spp_s = min(4, cfg["spp"])
     # size the sample for ~budget_s of CPU work: grow the row band (then the spp) until one render takes >= budget/3
     fp = frame_for(scene, cfg, cfg["spp"], 0, spp_s)
     rows = 8
     while True:
         y0 = (H - rows) // 2
-        t = time.time(); o.render(fp, threads=0, rows=(y0, y0 + rows)); dt = max(time.time() - t, 1e-3)
+        t = time.time(); o.render(fp, threads=cores, rows=(y0, y0 + rows)); dt = max(time.time() - t, 1e-3)
         if dt >= budget_s / 3 or (rows >= H and spp_s >= cfg["spp"]):
             break
         grow = min(4.0, max(1.5, 0.8 * budget_s / dt))
@@ -130,7 +131,7 @@ def cpu_arm(scene, cfg, budget_s=15.0, steps=1, warmup=0):
     y0 = (H - rows) // 2
     vals, last = [], None
     for i in range(warmup + steps):
-        r = o.render(fp, threads=0, rows=(y0, y0 + rows))
+        r = o.render(fp, threads=cores, rows=(y0, y0 + rows))
         rays = r["rays_extend"] + r["rays_shadow"]
         if i >= warmup:
             vals.append(rays / r["seconds"] / 1e6)
