@@ -30,6 +30,23 @@ __global__ void k_tri_inst(const uint32_t* __restrict__ prim_offsets, uint32_t n
     tri_inst[t] = lo;
 }
 
+__global__ void k_libm_eval(int fn, const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out, uint64_t n) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float x = a[i], y = b ? b[i] : 0.0f;
+    float r = 0.0f;
+    switch (fn) {
+        case 0: r = hj_sinf(x); break;
+        case 1: r = hj_cosf(x); break;
+        case 2: r = hj_acosf(x); break;
+        case 3: r = hj_logf(x); break;
+        case 4: r = hj_expf(x); break;
+        case 5: r = hj_powf(x, y); break;
+        default: r = hj_atan2f(x, y); break;
+    }
+    out[i] = r;
+}
+
 extern "C" {
 
 int hj_abi_version(void) { return HJ_ABI_VERSION; }
@@ -119,7 +136,7 @@ int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
     return HJ_OK;
 }
 
-static float srgb_to_linear(float v) { return (v <= 0.04045f) ? v / 12.92f : powf((v + 0.055f) / 1.055f, 2.4f); }
+static float srgb_to_linear(float v) { return (v <= 0.04045f) ? v / 12.92f : hjm_powf((v + 0.055f) / 1.055f, 2.4f); }   // hj_libm.h: same table as the oracle's
 
 int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
     if (!c) return HJ_ERR_INVALID;
@@ -344,6 +361,24 @@ int hj_finalize(hj_ctx* c) {
     int rc = hj_wavefront_finalize(c);
     if (rc) return rc;
     HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    return HJ_OK;
+}
+
+int hj_libm_eval(hj_ctx* c, int fn, const float* a, const float* b, float* out, uint64_t n) {
+    if (!c || !a || !out) return HJ_ERR_INVALID;
+    HJ_REQUIRE(c, fn >= 0 && fn <= 6, HJ_ERR_INVALID, "hj_libm_eval: fn must be 0..6");
+    HJ_REQUIRE(c, fn < 5 || b, HJ_ERR_INVALID, "hj_libm_eval: binary function needs b");
+    if (n == 0) return HJ_OK;
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    DevBuf da, db, dout;
+    HJ_CUDA(c, da.reserve(n * 4)); HJ_CUDA(c, dout.reserve(n * 4));
+    HJ_CUDA(c, cudaMemcpyAsync(da.p, a, n * 4, cudaMemcpyHostToDevice, c->stream));
+    if (b) { HJ_CUDA(c, db.reserve(n * 4)); HJ_CUDA(c, cudaMemcpyAsync(db.p, b, n * 4, cudaMemcpyHostToDevice, c->stream)); }
+    k_libm_eval<<<(uint32_t)((n + 255) / 256), 256, 0, c->stream>>>(fn, da.as<float>(), b ? db.as<float>() : nullptr, dout.as<float>(), n);
+    HJ_CUDA(c, cudaMemcpyAsync(out, dout.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    HJ_CUDA(c, cudaGetLastError());
+    da.release(); db.release(); dout.release();
     return HJ_OK;
 }
 

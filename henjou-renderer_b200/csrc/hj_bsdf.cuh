@@ -47,7 +47,7 @@ struct Disney {
     HJ_DI static float cc_D(const float3& wm, float a) {                                            // :131-139
         float a2 = a * a;
         float t = 1.0f + (a2 - 1.0f) * wm.y * wm.y;
-        return (a2 - 1.0f) / (HJ_PI * logf(a2) * t);
+        return (a2 - 1.0f) / (HJ_PI * hj_logf(a2) * t);
     }
     HJ_DI static float cc_Lambda(const float3& w, float a) {                                        // :126-129
         float t1 = 1.0f + (a * a * w.x * w.x + a * a * w.z * w.z) / (w.y * w.y);

@@ -4,18 +4,24 @@
 // SURVEY §8a): each function cites the lines it follows.
 #pragma once
 #include "hj_vec.cuh"
+#include "hj_libm.h"
 #include <float.h>
 
 #define HJ_PI 3.14159265358979323846f       // common/constant.h:3
 #define HJ_TWO_PI 6.28318530717958647692f   // common/constant.h:4
 #define HJ_INV_PI 0.31830988618379067154f   // common/constant.h:6
 
-// One copy of each libm routine the shading code calls (they inline to 50-200 instructions apiece; k_shade calls them
-// from ~40 sites and must stay inside the instruction cache). Same functions, same results.
-static HJ_NI float hj_powf(float a, float b) { return powf(a, b); }
-static HJ_NI float hj_sinf(float a) { return sinf(a); }
-static HJ_NI float hj_cosf(float a) { return cosf(a); }
-static HJ_NI float hj_acosf(float a) { return acosf(a); }
+// The elementary functions are the shared ones of hj_libm.h (same bits as the CPU oracle build, which includes the same
+// header). One out-of-line copy of each: they are 60-150 instructions apiece, the shading kernels call them from ~40 sites
+// and must stay inside the instruction cache.
+static HJ_NI float hj_powf(float a, float b) { return hjm_powf(a, b); }
+static HJ_NI float hj_sinf(float a) { return hjm_sinf(a); }
+static HJ_NI float hj_cosf(float a) { return hjm_cosf(a); }
+static HJ_NI void hj_sincosf(float a, float& s, float& c) { hjm_sincosf(a, s, c); }
+static HJ_NI float hj_acosf(float a) { return hjm_acosf(a); }
+static HJ_NI float hj_logf(float a) { return hjm_logf(a); }
+static HJ_NI float hj_expf(float a) { return hjm_expf(a); }
+static HJ_NI float hj_atan2f(float y, float x) { return hjm_atan2f(y, x); }
 
 // cmj.h:38-51 xxhash32(uint4)
 HJ_DI uint32_t xxhash32_u4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
@@ -160,8 +166,8 @@ HJ_DI float uchimura1(float x, float P, float a, float m, float l, float c, floa
     float w0 = 1.0 - smoothstep1(0.0, m, x);
     float w2 = step1(m + l0, x);
     float w1 = 1.0 - w0 - w2;
-    float T = m * powf(x / m, c) + b;
-    float S = P - (P - S1) * expf(CP * (x - S0));
+    float T = m * hj_powf(x / m, c) + b;
+    float S = P - (P - S1) * hj_expf(CP * (x - S0));
     float L = m + a * (x - m);
     return T * w0 + L * w1 + S * w2;
 }
@@ -178,7 +184,7 @@ HJ_DI float3 tonemap_aces(float3 x) {
 // renderer.h:73-85 toSRGB + quantizeUnsignedChar (host code in the reference; done on the device here)
 HJ_DI float3 to_srgb(const float3& col) {
     float ig = 1.0f / 2.4f;
-    float3 p = f3(powf(col.x, ig), powf(col.y, ig), powf(col.z, ig));
+    float3 p = f3(hj_powf(col.x, ig), hj_powf(col.y, ig), hj_powf(col.z, ig));
     return f3(col.x < 0.0031308f ? 12.92f * col.x : 1.055f * p.x - 0.055f,
               col.y < 0.0031308f ? 12.92f * col.y : 1.055f * p.y - 0.055f,
               col.z < 0.0031308f ? 12.92f * col.z : 1.055f * p.z - 0.055f);

@@ -32,7 +32,7 @@ struct DevScene {
     float4* tri_pos;     // 3 per triangle, by global primitive id
     float4* tri_attr;    // 4 per triangle: (n0,u0) (n1,v0) (n2,u1) (v1,u2,v2,material id)
     // acceleration structure
-    const uint4* nodes;  // 5 x 16 B per 8-wide node
+    const uint4* nodes;  // 7 x 16 B (112 B) per 8-wide node, layout in hj_trace.cuh
     const float4* btris; // 3 per triangle in leaf order, v0.w = global primitive id
 };
 
@@ -77,9 +77,9 @@ static HJ_NI float3 sky_radiance(const DevScene& S, const float3& dir, float ibl
     float4 c;
     if (S.ibl_w == 1 && S.ibl_h == 1) c = S.ibl[0];
     else {
-        float phi = atan2f(dir.z, dir.x);
+        float phi = hj_atan2f(dir.z, dir.x);
         if (phi < 0.0f) phi += 2.0f * M_PIf;
-        float theta = acosf(clampf(dir.y, -1.0f, 1.0f));
+        float theta = hj_acosf(clampf(dir.y, -1.0f, 1.0f));
         float u = phi * (1.0f / (2.0f * M_PIf)), v = theta * (1.0f / M_PIf);
         float xb = u * (float)S.ibl_w - 0.5f, yb = v * (float)S.ibl_h - 0.5f;
         float fx = floorf(xb), fy = floorf(yb);

@@ -47,6 +47,7 @@ def load_library():
     L.hj_get_stats.argtypes = [vp, C.POINTER(abi.hj_stats)]
     L.hj_trace.argtypes = [vp, abi.f32p, C.c_uint64, C.c_int, abi.u32p, abi.f32p]
     L.hj_post.argtypes = [vp, C.c_int]
+    L.hj_libm_eval.argtypes = [vp, C.c_int, abi.f32p, abi.f32p, abi.f32p, C.c_uint64]
     L.hj_host_pin.argtypes = [vp, vp, C.c_size_t]
     L.hj_host_unpin.argtypes = [vp, vp]
     L.hj_comm_unique_id.argtypes = [vp]
@@ -144,6 +145,17 @@ class Renderer:
         self._check(self.L.hj_trace(self.ctx, rays.ctypes.data_as(abi.f32p), n, int(any_hit), prim.ctypes.data_as(abi.u32p),
                                     tuv.ctypes.data_as(abi.f32p)), "hj_trace")
         return prim, tuv
+
+    LIBM_FN = {"sinf": 0, "cosf": 1, "acosf": 2, "logf": 3, "expf": 4, "powf": 5, "atan2f": 6}
+
+    def libm(self, fn, a, b=None):
+        """Evaluates one elementary function of csrc/hj_libm.h on the device (hj_libm_eval)."""
+        a = np.ascontiguousarray(a, np.float32)
+        b = None if b is None else np.ascontiguousarray(b, np.float32)
+        out = np.empty_like(a)
+        self._check(self.L.hj_libm_eval(self.ctx, self.LIBM_FN[fn], a.ctypes.data_as(abi.f32p), b.ctypes.data_as(abi.f32p) if b is not None else None,
+                                        out.ctypes.data_as(abi.f32p), a.size), "hj_libm_eval")
+        return out
 
     # ---- multi-GPU (SURVEY §8e) ----
     @staticmethod

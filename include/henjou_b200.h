@@ -225,6 +225,12 @@ int hj_get_stats(hj_ctx* ctx, hj_stats* out);
  * hit (ties on t -> lower id) or 0xffffffff; any_hit: 1 / 0xffffffff. tuv: 3 floats per ray (t,b1,b2), may be NULL. */
 int hj_trace(hj_ctx* ctx, const float* rays, uint64_t n, int any_hit, uint32_t* prim, float* tuv);
 
+/* Diagnostic: evaluates one elementary function of csrc/hj_libm.h ON THE DEVICE over n HOST floats (fn 0 sinf, 1 cosf,
+ * 2 acosf, 3 logf, 4 expf, 5 powf(a,b), 6 atan2f(a,b); b may be NULL for the unary ones). The shading kernels call these
+ * instead of CUDA's libm (the reference calls libm at disneyBRDF.h:30-38,64-80,93-100,131-139, BSDFs.h:551-586, math.h:26-37,
+ * color.h:10-29, renderer.h:73-85); the same header compiled for the host gives the same bits (tests/test_gpu_libm.py). */
+int hj_libm_eval(hj_ctx* ctx, int fn, const float* a, const float* b, float* out, uint64_t n);
+
 /* Multi-GPU: sample-slice data parallelism, replicated scene, one sum-reduction of the
  * float4 accumulation buffer per frame over NCCL/NVLink. unique_id is the 128-byte ncclUniqueId. */
 int hj_comm_unique_id(void* unique_id_128);

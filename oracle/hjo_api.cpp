@@ -61,6 +61,31 @@ int hjo_trace(hjo_ctx* c, const float* rays, uint64_t n, int anyhit, uint32_t* p
     return trace_batch(c->c, rays, n, anyhit, prim, tuv);
 }
 
+int hjo_path_events(hjo_ctx* c, const hj_frame_params* fp, uint32_t pixel, uint32_t sample, void* events, uint32_t cap, float* radiance3) {
+    if (!c || !fp) return HJ_ERR_INVALID;
+    return path_events<RestatedPolicy>(c->c, *fp, pixel, sample, (hjo_event*)events, cap, radiance3);
+}
+int hjo_kat_libm(int fn, const float* a, const float* b, float* out, uint64_t n) {
+    for (uint64_t i = 0; i < n; i++) {
+        switch (fn) {
+            case 0: out[i] = hjo_sinf(a[i]); break;
+            case 1: out[i] = hjo_cosf(a[i]); break;
+            case 2: out[i] = hjo_acosf(a[i]); break;
+            case 3: out[i] = hjo_logf(a[i]); break;
+            case 4: out[i] = hjo_expf(a[i]); break;
+            case 5: out[i] = hjo_powf(a[i], b[i]); break;
+            case 6: out[i] = hjo_atan2f(a[i], b[i]); break;
+            default: return HJ_ERR_INVALID;
+        }
+    }
+    return HJ_OK;
+}
+#ifdef HJO_GLIBC_LIBM
+int hjo_libm_kind(void) { return 1; }
+#else
+int hjo_libm_kind(void) { return 0; }
+#endif
+
 uint32_t hjo_kat_xxhash32(uint32_t p) { return xxhash32_u(p); }
 uint32_t hjo_kat_xxhash32_u4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) { return xxhash32_u4(x, y, z, w); }
 uint32_t hjo_kat_permute(uint32_t i, uint32_t l, uint32_t p) { return permute(i, l, p); }

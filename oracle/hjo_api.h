@@ -45,6 +45,15 @@ int hjo_render(hjo_ctx*, const hj_frame_params*, int n_threads, uint32_t y0, uin
 /* rays: 8 floats each (ox,oy,oz,tmin, dx,dy,dz,tmax). prim: ~0 on miss. tuv: 3 floats per ray (t,b1,b2). */
 int hjo_trace(hjo_ctx*, const float* rays, uint64_t n, int any_hit, uint32_t* prim, float* tuv);
 
+/* Decision trace of one path (pixel index, global sample index): events {kind, outcome, a, b} (4 x 32 bit each; kinds in
+ * hjo_vec.h) in path order, at most cap stored; returns the number produced or a negative hj_status. The reference-headers
+ * build records closest-hit / shadow events only (its BSDF code is the reference's, unmodified). */
+int hjo_path_events(hjo_ctx*, const hj_frame_params*, uint32_t pixel, uint32_t sample, void* events, uint32_t cap, float* radiance3);
+/* elementary functions as this build evaluates them: fn 0 sinf, 1 cosf, 2 acosf, 3 logf, 4 expf, 5 powf(a,b), 6 atan2f(a,b) */
+int hjo_kat_libm(int fn, const float* a, const float* b, float* out, uint64_t n);
+/* 0: the shared portable implementations of hj_libm.h (bit-identical to the CUDA kernels), 1: glibc */
+int hjo_libm_kind(void);
+
 /* ---- known-answer entry points (SURVEY §8c KAT block) ---- */
 uint32_t hjo_kat_xxhash32(uint32_t p);
 uint32_t hjo_kat_xxhash32_u4(uint32_t x, uint32_t y, uint32_t z, uint32_t w);

@@ -43,7 +43,7 @@ struct Disney {
         float phi = 2.0f * kPi * uv.x;
         float z = fmaf((1.0f - uv.y), (1.0f + swo.y), -swo.y);
         float st = sqrtf(clamp(1.0f - z * z, 0.0f, 1.0f));
-        float x = st * cosf(phi), y = st * sinf(phi);
+        float x = st * hjo_cosf(phi), y = st * hjo_sinf(phi);
         float3 h = make_float3(x, z, y) + swo;
         return normalize(make_float3(h.x * alpha, h.y, h.z * alpha));
     }
@@ -53,7 +53,7 @@ struct Disney {
     static float cc_D(const float3& wm, float a) {                                                    // :131-139
         float a2 = a * a;
         float t = 1.0f + (a2 - 1.0f) * wm.y * wm.y;
-        return (a2 - 1.0f) / (kPi * logf(a2) * t);
+        return (a2 - 1.0f) / (kPi * hjo_logf(a2) * t);
     }
     static float cc_Lambda(const float3& w, float a) {                                                // :126-129
         float t1 = 1.0f + (a * a * w.x * w.x + a * a * w.z * w.z) / (w.y * w.y);
@@ -63,10 +63,10 @@ struct Disney {
         return cc_D(wm, cc_alpha) * fabsf(wm.y) / (4.0f * fabsf(dot(wm, wo)));
     }
     float3 sample_clearcoat(const float2& uv, const float3& wo, float& pdf) const {                   // :93-100
-        float ct = sqrtf(fmaxf((1.0f - powf(cc_alpha * cc_alpha, 1.0f - uv.x)) / (1.0f - cc_alpha * cc_alpha), 0.0f));
+        float ct = sqrtf(fmaxf((1.0f - hjo_powf(cc_alpha * cc_alpha, 1.0f - uv.x)) / (1.0f - cc_alpha * cc_alpha), 0.0f));
         float st = sqrtf(fmaxf(1.0f - ct * ct, 0.0f));
         float phi = kTwoPi * uv.y;
-        float3 wm = make_float3(cosf(phi) * st, ct, sinf(phi) * st);
+        float3 wm = make_float3(hjo_cosf(phi) * st, ct, hjo_sinf(phi) * st);
         pdf = pdf_clearcoat(wm, wo);
         return wm;
     }
@@ -118,16 +118,16 @@ struct Disney {
         float sel = draw1(st);
         float pd = 1.0f, ps = 1.0f, pc = 1.0f;
         float2 xi = draw2(st);
-        if (sel < dw) {
-            float theta = 0.5f * acosf(1.0f - 2.0f * xi.x);    // sampleDiffuse :30-38
+        if (hjo_lt(HJO_EV_LOBE_DIFFUSE, sel, dw)) {
+            float theta = 0.5f * hjo_acosf(1.0f - 2.0f * xi.x);    // sampleDiffuse :30-38
             float phi = 2.0f * M_PIf * xi.y;
-            float ct = cosf(theta), sn = sinf(theta);
-            wi = make_float3(cosf(phi) * sn, ct, sinf(phi) * sn);
+            float ct = hjo_cosf(theta), sn = hjo_sinf(theta);
+            wi = make_float3(hjo_cosf(phi) * sn, ct, hjo_sinf(phi) * sn);
             pd = pdf_diffuse(wi);
             float3 wm = normalize(wi + wo);
             ps = pdf_specular(wm, wo);
             pc = pdf_clearcoat(wm, wo);
-        } else if (sel < dw + sw) {
+        } else if (hjo_lt(HJO_EV_LOBE_SPECULAR, sel, dw + sw)) {
             float3 wm = sample_vndf(xi, wo);
             ps = pdf_specular(wm, wo);
             wi = reflect(-wo, wm);
@@ -140,7 +140,7 @@ struct Disney {
             ps = pdf_specular(wm, wo);
         }
         pdf = dw * pd + sw * ps + cw * pc;
-        if (wi.y < 0.0) { pdf = 1.0f; return make_float3(0.0f); }
+        if (hjo_lt(HJO_EV_BELOW_HORIZON, wi.y, 0.0f)) { pdf = 1.0f; return make_float3(0.0f); }
         return eval(wo, wi);
     }
     // :309-326
@@ -161,11 +161,11 @@ static inline float3 glass_sample(const float3& rho, float ior, bool negative, c
     float ior_o = 1.0, ior_i = ior, sign = 1.0;
     float3 lwo = wo, lwi = make_float3(0.0f);
     float3 n = make_float3(0, 1, 0);
-    if (wo.y < 0.0) { ior_o = ior; ior_i = 1.0; lwo.y = -lwo.y; sign = -1.0; }
+    if (hjo_lt(HJO_EV_GLASS_INSIDE, wo.y, 0.0f)) { ior_o = ior; ior_i = 1.0; lwo.y = -lwo.y; sign = -1.0; }
     const float fr = schlick_ior(ior_o, ior_i, lwo, n);
     float3 f;
     float p = draw1(st);
-    if (p < fr) {
+    if (hjo_lt(HJO_EV_GLASS_FRESNEL, p, fr)) {
         lwi = reflect(-lwo, n); pdf = 1; f = rho / fabsf(lwi.y);
     } else {
         float3 t;
@@ -196,22 +196,22 @@ struct MultiScatterGGX {
     float G1_height(const float3& w, float h0) const {                                                            // :551-563
         if (w.y > 0.9999f) return 1.0f;
         if (w.y <= 0.0f) return 0.0f;
-        return powf(C1(h0), Lambda(w));
+        return hjo_powf(C1(h0), Lambda(w));
     }
     float sample_height(const float3& wr, float hr, float U) const {                                              // :566-586
-        if (wr.y > 0.9999f) return FLT_MAX;
-        if (wr.y < -0.9999f) return invC1(U * C1(hr));
-        if (fabsf(wr.y) < 0.0001f) return hr;
+        if (hjo_gt(HJO_EV_GGX_UP, wr.y, 0.9999f)) return FLT_MAX;
+        if (hjo_lt(HJO_EV_GGX_DOWN, wr.y, -0.9999f)) return invC1(U * C1(hr));
+        if (hjo_lt(HJO_EV_GGX_GRAZING, fabsf(wr.y), 0.0001f)) return hr;
         const float g = G1_height(wr, hr);
-        if (U > 1.0f - g) return FLT_MAX;
-        return invC1(C1(hr) / powf((1.0f - U), 1.0f / Lambda(wr)));
+        if (hjo_gt(HJO_EV_GGX_ESCAPE, U, 1.0f - g)) return FLT_MAX;
+        return invC1(C1(hr) / hjo_powf((1.0f - U), 1.0f / Lambda(wr)));
     }
     float3 sample_vndf(const float2& uv, const float3& wo) const {                                                // :616-632
         float3 swo = normalize(make_float3(wo.x * alpha, wo.y, wo.z * alpha));
         float phi = 2.0f * kPi * uv.x;
         float z = fmaf((1.0f - uv.y), (1.0f + swo.y), -swo.y);
         float st = sqrtf(clamp(1.0f - z * z, 0.0f, 1.0f));
-        float x = st * cosf(phi), y = st * sinf(phi);
+        float x = st * hjo_cosf(phi), y = st * hjo_sinf(phi);
         float3 h = make_float3(x, z, y) + swo;
         return normalize(make_float3(h.x * alpha, h.y, h.z * alpha));
     }
@@ -246,7 +246,7 @@ struct MultiScatterGGX {
     float3 sample(const float3& wo, float3& wi, Sampler& st, float& pdf) const {
         int order;
         float3 f = walk(wo, wi, order, st);
-        if (wi.y < 0.0 || order > 5) return make_float3(0.0f);
+        if (hjo_lt(HJO_EV_GGX_BELOW, wi.y, 0.0f) || order > 5) return make_float3(0.0f);
         pdf = fabsf(wi.y);
         return f;
     }

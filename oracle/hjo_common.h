@@ -42,7 +42,7 @@ struct ImageF { std::vector<float4> px; int w = 0, h = 0; };
 
 // sRGB EOTF as the texture unit applies it per texel before filtering (renderer.h:785).
 static inline float srgb_to_linear(float c) {
-    return (c <= 0.04045f) ? c / 12.92f : powf((c + 0.055f) / 1.055f, 2.4f);
+    return (c <= 0.04045f) ? c / 12.92f : hjo_powf((c + 0.055f) / 1.055f, 2.4f);
 }
 static inline int wrapi(int i, int n) { int r = i % n; return r < 0 ? r + n : r; }
 
@@ -333,9 +333,9 @@ static inline bool any_hit(const Scene& S, const float3& o, const float3& d, flo
 
 // D6: equirect sky lookup, y-up. u = phi/2pi with phi = atan2(z,x) in [0,2pi), v = acos(y)/pi.
 static inline float3 sky_radiance(const Scene& S, const float3& dir, float ibl_intensity) {
-    float phi = atan2f(dir.z, dir.x);
+    float phi = hjo_atan2f(dir.z, dir.x);
     if (phi < 0.0f) phi += 2.0f * M_PIf;
-    float theta = acosf(clamp(dir.y, -1.0f, 1.0f));
+    float theta = hjo_acosf(clamp(dir.y, -1.0f, 1.0f));
     float4 c = bilinearF(S.ibl, phi * (1.0f / (2.0f * M_PIf)), theta * (1.0f / M_PIf));
     return ibl_intensity * make_float3(c);
 }

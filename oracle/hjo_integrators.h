@@ -20,6 +20,7 @@ static inline float3 sample_light(Sampler& st, float& pdf, float3& normal, float
     float p = draw1(st);
     int index = (int)(p * count);
     if (index == count) index--;
+    if (g_hjo_events) hjo_note(HJO_EV_LIGHT_PICK, (uint32_t)index, p * count, (float)index);
     unsigned int prim = S.light_prim_ids[index];
     // binary search of the owning instance (:26-38), kept verbatim in behaviour incl. unsigned wrap
     unsigned int left = 0U, right = (unsigned int)S.prim_offsets.size() - 1, middle = (left + right) / 2U;
@@ -65,7 +66,7 @@ static inline float3 integrate_pt(float3 o, float3 d, Sampler st, float3& aov_al
     float3 L = {0, 0, 0}, thr = {1, 1, 1};
     for (int depth = 0; depth < max_depth; depth++) {
         float rp = fmaxf(thr.x, fmaxf(thr.y, thr.z));
-        if (rp < draw1(st)) break;
+        if (hjo_lt(HJO_EV_ROULETTE, rp, draw1(st))) break;
         thr /= rp;
         g_trace.traced_extend++;
         Surface prd = trace_extend(o, d, 0.001f, 1e16f);
@@ -91,7 +92,7 @@ static inline float3 integrate_nee(float3 o, float3 d, Sampler st, float3& aov_a
     float3 L = {0, 0, 0}, thr = {1, 1, 1};
     for (int depth = 0; depth < max_depth; depth++) {
         float rp = fmaxf(thr.x, fmaxf(thr.y, thr.z));
-        if (rp < draw1(st)) break;
+        if (hjo_lt(HJO_EV_ROULETTE, rp, draw1(st))) break;
         thr /= rp;
         g_trace.traced_extend++;
         Surface prd = trace_extend(o, d, 0.001f, 1e16f);
@@ -138,7 +139,7 @@ static inline float3 integrate_mis(const float3& o0, const float3& d0, Sampler& 
     const bool have_lights = !g_trace.scene->light_prim_ids.empty();
     for (int depth = 0; depth < max_depth; depth++) {
         float rp = fmaxf(thr.x, fmaxf(thr.y, thr.z));
-        if (rp < draw1(st)) break;
+        if (hjo_lt(HJO_EV_ROULETTE, rp, draw1(st))) break;
         thr /= rp;
         g_trace.traced_extend++;
         Surface prd = trace_extend(o, d, 0.001f, 1e16f);

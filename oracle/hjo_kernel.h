@@ -99,22 +99,22 @@ static inline float draw1(Sampler& s) { return draw2(s).x; }
 // math.h:7-15
 static inline float3 cosine_sample(float u, float v, float& pdf) {
     float phi = 2.0f * M_PIf * v;
-    float theta = 0.5f * acosf(1.0f - 2.0f * u);
-    float ct = cosf(theta), st = sinf(theta);
+    float theta = 0.5f * hjo_acosf(1.0f - 2.0f * u);
+    float ct = hjo_cosf(theta), st = hjo_sinf(theta);
     pdf = ct / M_PIf;
-    return make_float3(cosf(phi) * st, ct, sinf(phi) * st);
+    return make_float3(hjo_cosf(phi) * st, ct, hjo_sinf(phi) * st);
 }
 // math.h:26-29
 static inline float3 schlick3(const float3& F0, const float3& w, const float3& n) {
     float term1 = 1.0f - dot(w, n);
-    return (1.0f - F0) * powf(term1, 5.0f) + F0;
+    return (1.0f - F0) * hjo_powf(term1, 5.0f) + F0;
 }
 // math.h:31-37
 static inline float schlick_ior(float no, float ni, const float3& w, const float3& n) {
     float F0 = (no - ni) / (no + ni);
     F0 = F0 * F0;
     float term1 = 1.0f - dot(w, n);
-    return F0 + (1.0f - F0) * powf(term1, 5.0f);
+    return F0 + (1.0f - F0) * hjo_powf(term1, 5.0f);
 }
 // math.h:43-51
 static inline void onb(const float3& n, float3& t, float3& b) {
@@ -138,7 +138,7 @@ static inline float norm2(const float3& v) { return v.x * v.x + v.y * v.y + v.z 
 // math.h:92-103
 static inline bool refract_dir(const float3& v, const float3& n, float ior1, float ior2, float3& r) {
     const float3 t_h = -ior1 / ior2 * (v - dot(v, n) * n);
-    if (norm2(t_h) > 1.0f) return false;
+    if (hjo_gt(HJO_EV_GLASS_TIR, norm2(t_h), 1.0f)) return false;
     const float3 t_p = -sqrtf(fmaxf(1.0f - norm2(t_h), 0.0f)) * n;
     r = t_h + t_p;
     return true;
@@ -167,8 +167,8 @@ static inline float uchimura1(float x, float P, float a, float m, float l, float
     float w0 = 1.0 - smoothstep1(0.0, m, x);
     float w2 = step1(m + l0, x);
     float w1 = 1.0 - w0 - w2;
-    float T = m * powf(x / m, c) + b;
-    float S = P - (P - S1) * expf(CP * (x - S0));
+    float T = m * hjo_powf(x / m, c) + b;
+    float S = P - (P - S1) * hjo_expf(CP * (x - S0));
     float L = m + a * (x - m);
     return T * w0 + L * w1 + S * w2;
 }
@@ -185,7 +185,7 @@ static inline float3 tonemap_aces(float3 x) {
 // renderer.h:73-85 host toSRGB + quantizeUnsignedChar
 static inline float3 to_srgb(const float3& col) {
     float ig = 1.0f / 2.4f;
-    float3 p = make_float3(powf(col.x, ig), powf(col.y, ig), powf(col.z, ig));
+    float3 p = make_float3(hjo_powf(col.x, ig), hjo_powf(col.y, ig), hjo_powf(col.z, ig));
     return make_float3(col.x < 0.0031308f ? 12.92f * col.x : 1.055f * p.x - 0.055f,
                        col.y < 0.0031308f ? 12.92f * col.y : 1.055f * p.y - 0.055f,
                        col.z < 0.0031308f ? 12.92f * col.z : 1.055f * p.z - 0.055f);

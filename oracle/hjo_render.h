@@ -96,6 +96,34 @@ static int render_rows(Context& C, const hj_frame_params& fp, int n_threads, uin
     return HJ_OK;
 }
 
+// One path (pixel, global sample index) with the decision trace switched on: the events of hjo_vec.h in order, and the
+// path's radiance. Returns the number of events the path produced (may exceed cap; only the first cap are stored).
+template <class Policy>
+static int path_events(Context& C, const hj_frame_params& fp, uint32_t pix, uint32_t s, hjo_event* ev, uint32_t cap, float* radiance3) {
+    if (!C.have_scene || !C.have_accel) return HJ_ERR_NO_ACCEL;
+    const uint32_t W = fp.width, H = fp.height;
+    if (W == 0 || H == 0 || pix >= W * H) return HJ_ERR_INVALID;
+    const float3 cpos = make_float3(fp.camera_pos[0], fp.camera_pos[1], fp.camera_pos[2]);
+    const float3 cdir = make_float3(fp.camera_dir[0], fp.camera_dir[1], fp.camera_dir[2]);
+    const float3 cup = make_float3(fp.camera_up[0], fp.camera_up[1], fp.camera_up[2]);
+    const float3 cright = make_float3(fp.camera_right[0], fp.camera_right[1], fp.camera_right[2]);
+    g_trace = TraceCtx(); g_trace.scene = &C.scene; g_trace.ibl_intensity = fp.ibl_intensity; g_shade.scene = &C.scene;
+    const uint32_t x = pix % W, y = pix / W;
+    typename Policy::State st = Policy::make((uint64_t)s, fp.frame, pix);
+    float jx = 0.0f, jy = 0.0f;
+    if (fp.pixel_jitter) { float2 xi = Policy::draw2(st); jx = xi.x; jy = xi.y; }
+    const float u = (2.0f * ((float)x + jx) - (float)W) / (float)H;
+    const float v = (2.0f * ((float)y + jy) - (float)H) / (float)H;
+    const float3 d = normalize(fp.camera_f * cdir + u * cright + v * cup);
+    HjoEventLog log{ev, cap, 0u};
+    g_hjo_events = &log;
+    float3 alb = make_float3(0.0f), nrm = make_float3(0.0f);
+    const float3 L = Policy::integrate(fp.integrator, cpos, d, st, alb, nrm, fp.max_depth);
+    g_hjo_events = nullptr;
+    if (radiance3) { radiance3[0] = L.x; radiance3[1] = L.y; radiance3[2] = L.z; }
+    return (int)log.n;
+}
+
 static inline int trace_batch(Context& C, const float* rays, uint64_t n, int anyhit, uint32_t* prim, float* tuv) {
     if (!C.have_accel) return HJ_ERR_NO_ACCEL;
 #pragma omp parallel for schedule(dynamic, 256)

@@ -34,6 +34,7 @@ static thread_local TraceCtx g_trace;
 static inline Surface trace_extend(const float3& o, const float3& d, float tmin, float tmax) {
     Hit h = closest_hit(*g_trace.scene, o, d, tmin, tmax);
     debug_note_extend(g_trace.dbg, h);
+    if (g_hjo_events) hjo_note(HJO_EV_HIT, h.hit ? h.prim : 0xffffffffu, h.hit ? fminf(fminf(h.b1, h.b2), 1.0f - h.b1 - h.b2) : 0.0f, h.hit ? h.t : 0.0f);
     g_trace.rays_extend++;
     return make_surface(*g_trace.scene, h, d, g_trace.ibl_intensity);
 }
@@ -41,7 +42,9 @@ static inline Surface trace_extend(const float3& o, const float3& d, float tmin,
 static inline bool trace_shadow(const float3& o, const float3& d, float tmin, float tmax) {
     g_trace.dbg.rays_shadow++;
     g_trace.rays_shadow++;
-    return any_hit(*g_trace.scene, o, d, tmin, tmax);
+    const bool occluded = any_hit(*g_trace.scene, o, d, tmin, tmax);
+    if (g_hjo_events) hjo_note(HJO_EV_SHADOW, occluded ? 1u : 0u, tmin, tmax);
+    return occluded;
 }
 
 }  // namespace hjo

@@ -12,6 +12,46 @@
 #include <cstdint>
 #include <algorithm>
 
+// Elementary functions of the shading code. Default build (libhjo.so): the portable implementations of the product's
+// henjou-renderer_b200/csrc/hj_libm.h — one source for kernel and oracle, so the GPU comparison is bit-exact.
+// -DHJO_GLIBC_LIBM (libhjo_glibc.so): glibc's, as the reference-headers build (_ref/libhjref.so) uses them; this build is the
+// bridge: it matches _ref to float rounding, and differs from the default build ONLY in these seven functions.
+#ifdef HJO_GLIBC_LIBM
+static inline float hjo_sinf(float x) { return sinf(x); }
+static inline float hjo_cosf(float x) { return cosf(x); }
+static inline float hjo_acosf(float x) { return acosf(x); }
+static inline float hjo_atan2f(float y, float x) { return atan2f(y, x); }
+static inline float hjo_logf(float x) { return logf(x); }
+static inline float hjo_expf(float x) { return expf(x); }
+static inline float hjo_powf(float x, float y) { return powf(x, y); }
+#else
+#include "../henjou-renderer_b200/csrc/hj_libm.h"
+static inline float hjo_sinf(float x) { return hjm_sinf(x); }
+static inline float hjo_cosf(float x) { return hjm_cosf(x); }
+static inline float hjo_acosf(float x) { return hjm_acosf(x); }
+static inline float hjo_atan2f(float y, float x) { return hjm_atan2f(y, x); }
+static inline float hjo_logf(float x) { return hjm_logf(x); }
+static inline float hjo_expf(float x) { return hjm_expf(x); }
+static inline float hjo_powf(float x, float y) { return hjm_powf(x, y); }
+#endif
+
+// ---- decision trace (hjo_path_events, tools/parity_margins.py): every discrete decision of ONE path together with the
+// two values it compared, so that two builds of this oracle that differ only in libm can be aligned event by event and the
+// first diverging decision of a mismatching path shown to sit within a few ulp of its threshold. Null outside that tool.
+struct hjo_event { uint32_t kind, outcome; float a, b; };
+struct HjoEventLog { hjo_event* ev; uint32_t cap, n; };
+static thread_local HjoEventLog* g_hjo_events = nullptr;
+enum { HJO_EV_ROULETTE = 1, HJO_EV_LOBE_DIFFUSE = 2, HJO_EV_LOBE_SPECULAR = 3, HJO_EV_BELOW_HORIZON = 4, HJO_EV_GLASS_INSIDE = 5,
+       HJO_EV_GLASS_FRESNEL = 6, HJO_EV_GLASS_TIR = 7, HJO_EV_GGX_UP = 8, HJO_EV_GGX_DOWN = 9, HJO_EV_GGX_GRAZING = 10,
+       HJO_EV_GGX_ESCAPE = 11, HJO_EV_GGX_BELOW = 12, HJO_EV_LIGHT_PICK = 13, HJO_EV_HIT = 20, HJO_EV_SHADOW = 21 };
+static inline void hjo_note(uint32_t kind, uint32_t outcome, float a, float b) {
+    HjoEventLog* L = g_hjo_events;
+    if (L && L->n < L->cap) L->ev[L->n] = hjo_event{kind, outcome, a, b};
+    if (L) L->n++;
+}
+static inline bool hjo_lt(uint32_t kind, float a, float b) { const bool r = a < b; if (g_hjo_events) hjo_note(kind, r, a, b); return r; }
+static inline bool hjo_gt(uint32_t kind, float a, float b) { const bool r = a > b; if (g_hjo_events) hjo_note(kind, r, a, b); return r; }
+
 struct float2 { float x, y; };
 struct float3 { float x, y, z; };
 struct float4 { float x, y, z, w; };

@@ -103,6 +103,30 @@ int hjo_trace(hjo_ctx* c, const float* rays, uint64_t n, int anyhit, uint32_t* p
     return hjo::trace_batch(c->c, rays, n, anyhit, prim, tuv);
 }
 
+int hjo_path_events(hjo_ctx* c, const hj_frame_params* fp, uint32_t pixel, uint32_t sample, void* events, uint32_t cap, float* radiance3) {
+    if (!c || !fp || fp->max_depth != 10) return HJ_ERR_INVALID;
+    bind_params(c->c.scene);
+    params.image_width = fp->width; params.image_height = fp->height; params.spp = fp->spp; params.frame = fp->frame;
+    params.ibl_intensity = fp->ibl_intensity;
+    return hjo::path_events<RefPolicy>(c->c, *fp, pixel, sample, (hjo_event*)events, cap, radiance3);
+}
+int hjo_kat_libm(int fn, const float* a, const float* b, float* out, uint64_t n) {      // glibc, as the reference's headers call it
+    for (uint64_t i = 0; i < n; i++) {
+        switch (fn) {
+            case 0: out[i] = sinf(a[i]); break;
+            case 1: out[i] = cosf(a[i]); break;
+            case 2: out[i] = acosf(a[i]); break;
+            case 3: out[i] = logf(a[i]); break;
+            case 4: out[i] = expf(a[i]); break;
+            case 5: out[i] = powf(a[i], b[i]); break;
+            case 6: out[i] = atan2f(a[i], b[i]); break;
+            default: return HJ_ERR_INVALID;
+        }
+    }
+    return HJ_OK;
+}
+int hjo_libm_kind(void) { return 1; }
+
 uint32_t hjo_kat_xxhash32(uint32_t p) { return xxhash32(p); }
 uint32_t hjo_kat_xxhash32_u4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) { return xxhash32(make_uint4(x, y, z, w)); }
 uint32_t hjo_kat_permute(uint32_t i, uint32_t l, uint32_t p) { return cmj_permute(i, l, p); }

@@ -53,16 +53,29 @@ def _load(path):
     L.hjo_kat_onb.argtypes = [abi.f32p, abi.f32p, abi.f32p]
     L.hjo_kat_tonemap.argtypes = [C.c_int, abi.f32p, abi.f32p]
     L.hjo_kat_to_srgb8.argtypes = [abi.f32p, abi.u8p]
+    L.hjo_path_events.argtypes = [C.c_void_p, C.POINTER(abi.hj_frame_params), C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32, abi.f32p]
+    L.hjo_kat_libm.argtypes = [C.c_int, abi.f32p, abi.f32p, abi.f32p, C.c_uint64]
     return L
 
 
 _libs = {}
 
 
+PATHS = {"restatement": "libhjo.so", "glibc": "libhjo_glibc.so", "reference": "_ref/libhjref.so"}
+LIBM_FN = {"sinf": 0, "cosf": 1, "acosf": 2, "logf": 3, "expf": 4, "powf": 5, "atan2f": 6}
+EVENT_DTYPE = np.dtype([("kind", np.uint32), ("outcome", np.uint32), ("a", np.float32), ("b", np.float32)])
+EVENT_NAMES = {1: "russian roulette", 2: "Disney lobe: diffuse?", 3: "Disney lobe: specular?", 4: "Disney wi below horizon", 5: "glass: inside?",
+               6: "glass: Fresnel reflect?", 7: "glass: total internal reflection", 8: "EC-GGX: wr.y > 0.9999", 9: "EC-GGX: wr.y < -0.9999",
+               10: "EC-GGX: grazing", 11: "EC-GGX: escape (U > 1 - G1)", 12: "EC-GGX: wi below horizon", 13: "light pick", 20: "closest hit",
+               21: "shadow ray"}
+
+
 def lib(kind="restatement"):
-    """kind: 'restatement' (oracle/libhjo.so) or 'reference' (oracle/_ref/libhjref.so; None if not built)."""
+    """kind: 'restatement' (oracle/libhjo.so: the restatement with the product's shared hj_libm.h, bit-comparable to the
+    kernels), 'glibc' (oracle/libhjo_glibc.so: the same restatement on glibc's libm, the bridge to the reference build) or
+    'reference' (oracle/_ref/libhjref.so: the reference's own headers; None if not built)."""
     if kind not in _libs:
-        path = os.path.join(ORACLE_DIR, "libhjo.so" if kind == "restatement" else "_ref/libhjref.so")
+        path = os.path.join(ORACLE_DIR, PATHS[kind])
         if not os.path.exists(path):
             try:
                 build_oracle()
@@ -74,6 +87,15 @@ def lib(kind="restatement"):
 
 def fp(a):
     return a.ctypes.data_as(abi.f32p)
+
+
+def libm(kind, fn, a, b=None):
+    """Evaluates one elementary function (LIBM_FN) as the oracle build `kind` does, over float32 arrays."""
+    a = np.ascontiguousarray(a, np.float32)
+    b = np.ascontiguousarray(b if b is not None else np.zeros_like(a), np.float32)
+    out = np.empty_like(a)
+    assert lib(kind).hjo_kat_libm(LIBM_FN[fn], fp(a), fp(b), fp(out), a.size) == 0
+    return out
 
 
 class Oracle:
@@ -120,6 +142,14 @@ class Oracle:
         tuv = np.zeros((n, 3), np.float32)
         assert self.L.hjo_trace(self.ctx, fp(rays), n, int(any_hit), prim.ctypes.data_as(abi.u32p), fp(tuv)) == 0
         return prim, tuv
+
+    def path_events(self, fparams, pixel, sample, cap=4096):
+        """Decision trace of one path: (structured array of events, radiance[3])."""
+        ev = np.zeros(cap, EVENT_DTYPE)
+        rad = np.zeros(3, np.float32)
+        n = self.L.hjo_path_events(self.ctx, C.byref(fparams), int(pixel), int(sample), ev.ctypes.data_as(C.c_void_p), cap, fp(rad))
+        assert n >= 0, n
+        return ev[:min(n, cap)], rad
 
     def close(self):
         if self.ctx:

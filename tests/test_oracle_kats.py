@@ -9,7 +9,7 @@ import pytest
 import oracle_binding as ob
 from oracle_binding import hjo_kat_surface, fp
 
-KINDS = ["restatement", "reference"]
+KINDS = ["restatement", "glibc", "reference"]
 
 
 def L(kind):
