@@ -10,12 +10,18 @@ A step = one whole frame (all pixels x all samples of this rank's slice) through
   e2e     : the same metric through the C ABI with HOST buffers, every step: hj_scene_upload (geometry H2D) +
             hj_accel_build (transforms H2D, BVH rebuild ≙ updateIASMatrix) + hj_render + hj_readback of the colour
             AOV and the RGBA8 image (D2H), wall clock.
-  roofline: traversal kernels (k_trace<0|1|2>): algorithmic bytes = 112 B x nodes fetched + 48 B x
-            triangles fetched (counters-enabled pass) / their summed launch durations (event pairs, separate pass).
+  roofline: traversal kernels (k_trace<0|1|3>): algorithmic bytes = 80 B x nodes fetched + 48 B x triangles fetched
+            (SURVEY §8d / BASELINE.md §4; counters-enabled pass) / their launch durations (event pairs, separate pass); the same
+            with the 112 B the node really occupies is printed beside it (frac_112B). `traffic` = DRAM bytes per traversal
+            launch and the L1/L2 hit rates, issue rate and lanes per instruction come from the committed ncu capture of the
+            same workload (profiles/r02_ncu_trace_<workload>.json, written by tools/ncu_summary.py --json).
   cpu_baseline: the reference's own device headers compiled for the host (oracle/_ref, kind "reference") or the
             CPU restatement (kind "port"), all host cores, on a bounded sample (pixel rows x few spp) of the workload.
-N > 1 (torchrun): each rank renders its own slice of 64 global sample indices for every pixel (weak scaling,
-replicated scene), then one NCCL all-reduce of the float4 accumulation buffer per frame, inside the timed region.
+N > 1 (torchrun): STRONG scaling by default — the fixed 64-spp frame is split into sample slices of 64/N global sample indices
+per rank (hj.sample_slice; replicated scene), one NCCL all-reduce of the float4 accumulation buffer per frame inside the timed
+region; the line says scaling "strong" at every N and carries the weak-scaling figure (64 spp per rank) as the extra key "weak".
+`--scaling weak` times the weak form as the headline instead. `--as-rank-of N` (one GPU) renders what ONE rank of an N-way
+strong split renders, to predict the split's efficiency without the box.
 `--impl reference` times the CPU reference arm only (rank 0)."""
 import argparse
 import json
@@ -163,8 +169,14 @@ def gpu_arm(args, rank, world, local_rank):
     accel_cold_ms = r.stats()["ms_accel"]          # first build of the context: includes the cudaMalloc of every builder buffer
     r.build_accel(xf, inv)
     accel_ms = r.stats()["ms_accel"]               # full rebuild into the buffers the context already owns (the per-frame cost)
-    # weak scaling: every rank renders `spp` samples; the frame has spp*world global sample indices
-    fp = frame_for(scene, cfg, *hj.weak_slice(spp, rank, world))
+    # strong scaling (default): the fixed frame of `spp` samples split into contiguous sample slices, one per rank;
+    # weak scaling: every rank renders `spp` samples of a frame with spp*world global sample indices
+    strong = args.scaling != "weak"
+    fp_weak = frame_for(scene, cfg, *hj.weak_slice(spp, rank, world))
+    fp_strong = frame_for(scene, cfg, spp, *hj.sample_slice(spp, rank, world))
+    if args.as_rank_of > 1:
+        fp_strong = frame_for(scene, cfg, spp, *hj.sample_slice(spp, 0, args.as_rank_of))
+    fp = fp_strong if strong else fp_weak
     if world > 1:
         import torch
         uid = [hj.Renderer.comm_unique_id() if rank == 0 else None]
@@ -177,47 +189,59 @@ def gpu_arm(args, rank, world, local_rank):
             dist.barrier()
             torch.cuda.synchronize()
 
-    def step():
+    def step(fp):
         r.render(fp, sync=False)
         if world > 1:
             r.comm_reduce()          # NCCL all-reduce of the accumulation buffer + finalize (syncs the stream)
         r.sync()
 
-    for _ in range(args.warmup):
-        step()
+    def timed(fp, steps, warmup):
+        """-> (seconds: max over ranks, rays: sum over ranks, launches: sum over ranks, wall, per-rank device ms list)"""
+        for _ in range(warmup):
+            step(fp)
+        barrier()
+        t0 = time.perf_counter()
+        dev_ms, rays, launches = 0.0, 0, 0
+        for _ in range(steps):
+            step(fp)
+            st = r.stats()
+            dev_ms += st["ms_render"]; rays += st["rays_extend"] + st["rays_shadow"]; launches += st["kernel_launches"]
+        barrier()
+        wall = time.perf_counter() - t0
+        # N = 1: CUDA events on the context stream. N > 1: barrier-bracketed wall clock (render + all-reduce + finalize), max over ranks
+        t_rank = wall if world > 1 else dev_ms / 1e3
+        if world > 1:
+            import torch
+            tt = torch.tensor([t_rank, float(rays), float(launches), dev_ms], dtype=torch.float64, device="cuda")
+            tmax = tt.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            tmin = tt.clone(); dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+            tsum = tt.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+            return float(tmax[0]), int(tsum[1]), int(tsum[2]), wall, (float(tmin[3]) / steps, float(tmax[3]) / steps)
+        return t_rank, rays, launches, wall, (dev_ms / steps, dev_ms / steps)
+
     clocks = ClockSampler(local_rank)
-    barrier()
-    t0 = time.perf_counter()
-    dev_ms, rays, launches = 0.0, 0, 0
-    for _ in range(args.steps):
-        step()
-        st = r.stats()
-        dev_ms += st["ms_render"]; rays += st["rays_extend"] + st["rays_shadow"]; launches += st["kernel_launches"]
-    barrier()
-    wall = time.perf_counter() - t0
+    t_all, rays_all, launches_all, wall, render_ms = timed(fp, args.steps, args.warmup)
     clk = clocks.stop()
-    # device time per rank = its render events (+ the all-reduce, covered by wall); take the max over ranks of wall
-    t_rank = wall if world > 1 else dev_ms / 1e3
-    if world > 1:
-        import torch
-        tt = torch.tensor([t_rank, float(rays), float(launches)], dtype=torch.float64, device="cuda")
-        tmax = tt.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = tt.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        t_all, rays_all, launches_all = float(tmax[0]), int(tsum[1]), int(tsum[2])
-    else:
-        t_all, rays_all, launches_all = t_rank, rays, launches
     value = rays_all / t_all / 1e6
     out = dict(metric="Mrays/s", value=round(value, 2), unit="Mrays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
-               ms_per_step=round(1e3 * t_all / args.steps, 3), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
+               ms_per_step=round(1e3 * t_all / args.steps, 3), higher_is_better=True, scaling="strong" if strong else "weak", vs_baseline=None, dtype="f32",
                data="synthetic", impl="ours",
-               config=dict(workload=desc, triangles=scene.n_triangles, width=W, height=H, spp_per_gpu=spp, max_depth=cfg["max_depth"],
-                           integrator="MIS", parallelism="sample slices, replicated scene, NCCL all-reduce of accum" if world > 1 else "single GPU",
+               config=dict(workload=desc, triangles=scene.n_triangles, width=W, height=H, spp_per_gpu=(fp.sample_end - fp.sample_begin), spp_frame=int(fp.spp),
+                           max_depth=cfg["max_depth"],
+                           integrator="MIS", parallelism=("sample slices of the fixed %d-spp frame, " % spp if strong else "%d spp per rank, " % spp) +
+                           "replicated scene, NCCL all-reduce of accum" if world > 1 else ("single GPU" if args.as_rank_of <= 1 else
+                                                                                        "single GPU rendering rank 0's slice of a %d-way strong split" % args.as_rank_of),
                            l2_policy="inputs larger than L2 (126 MB): %d passes of %.1f M paths in flight x ~280 B of path state rewritten every "
                                      "bounce + %.0f MB of BVH nodes and triangles" % (min(8, r.stats()["passes"]), spp * W * H / max(1, r.stats()["passes"]) / 1e6,
                                                                                      (r.stats()["bvh_nodes"] * r.stats()["bvh_node_bytes"] + scene.n_triangles * 48) / 1e6),
                            timing="CUDA events on the context stream (N=1) / barrier-bracketed wall clock incl. all-reduce, max over ranks (N>1)"),
-               spp_per_s=round(spp * world * args.steps / t_all, 3), rays_per_step=rays_all // args.steps,
+               spp_per_s=round(int(fp.spp) * args.steps / t_all, 3) if args.as_rank_of <= 1 else None, rays_per_step=rays_all // args.steps,
+               render_ms_per_rank_min_max=[round(x, 3) for x in render_ms],
                gpu_launches=launches_all, accel_build_ms=round(accel_ms, 3), accel_first_build_ms=round(accel_cold_ms, 3), clocks=clk, wall_s=round(wall, 3))
+    if world > 1 and strong:
+        # the weak-scaling figure beside it: every rank renders the full `spp` samples of a spp*N-sample frame
+        tw, rw, _, _, _ = timed(fp_weak, args.steps, 1)
+        out["weak"] = dict(value=round(rw / tw / 1e6, 2), unit="Mrays/s", ms_per_step=round(1e3 * tw / args.steps, 3), spp_per_gpu=spp, spp_frame=spp * world)
     # ---- e2e through the C ABI with host buffers, every rank: upload + BVH rebuild + render (+ all-reduce) + read-back
     h2d = scene.vertices.nbytes + scene.normals.nbytes + scene.texcoords.nbytes + scene.indices.nbytes + scene.material_ids.nbytes + \
         scene.prim_offsets.nbytes + xf.nbytes + inv.nbytes + (scene.lut.nbytes if scene.lut is not None else 0) + scene.ibl.nbytes
@@ -253,8 +277,10 @@ def gpu_arm(args, rank, world, local_rank):
         # ---- roofline of the traversal kernels: bytes from a counters pass, time from an event-pair pass
         r.set_option("count_fetches", 1); r.render(fp); sc = r.stats(); r.set_option("count_fetches", 0)
         r.set_option("time_stages", 1); r.render(fp); stt = r.stats(); r.set_option("time_stages", 0)
-        node_bytes = float(sc["bvh_node_bytes"])          # 112: seven 16-byte words per 8-wide node
-        algo = node_bytes * sc["nodes_fetched"] + 48.0 * sc["tris_fetched"]
+        # SURVEY §8d / BASELINE.md §4: B_ray = 80 N_node + 48 N_tri (the 80-B node that was planned). The node built here is 112 B
+        # (the eight child masks moved into it); that figure is printed beside the headline as frac_112B.
+        algo = 80.0 * sc["nodes_fetched"] + 48.0 * sc["tris_fetched"]
+        algo112 = float(sc["bvh_node_bytes"]) * sc["nodes_fetched"] + 48.0 * sc["tris_fetched"]
         nrays = sc["rays_extend"] + sc["rays_shadow"]
         peaks = {}
         try:
@@ -271,16 +297,32 @@ def gpu_arm(args, rank, world, local_rank):
         n_trace_launches = n_types * cfg["max_depth"] * max(1, stt["passes"])
         ach = algo / (share * step_ms / 1e3) / 1e9
         ach_serial = algo / (stt["ms_trace"] / 1e3) / 1e9
-        out["roofline"] = dict(bound="hbm", achieved=round(ach, 1), peak=peak, unit="GB/s", frac=round(ach / peak, 4), traffic=None,
+        ach112 = algo112 / (share * step_ms / 1e3) / 1e9
+        # measured DRAM traffic and the counters that say what bounds the kernel: from the committed ncu capture of this workload
+        ncu, ncu_path = {}, os.path.join(ROOT, "profiles", "r02_ncu_trace_%s.json" % args.workload)
+        try:
+            ncu = json.load(open(ncu_path))
+        except Exception:
+            pass
+        tr = ncu.get("traversal", {})
+        out["roofline"] = dict(bound="hbm", achieved=round(ach, 1), peak=peak, unit="GB/s", frac=round(ach / peak, 4),
+                               traffic=tr.get("dram_bytes_per_launch"), traffic_source=os.path.relpath(ncu_path, ROOT) if tr else None,
+                               traffic_note=tr.get("note"),
+                               frac_112B=round(ach112 / peak, 4), achieved_112B=round(ach112, 1),
+                               dram_gbs_ncu=tr.get("dram_gbs"), dram_frac_of_peak_ncu=round(tr["dram_gbs"] / peak, 4) if tr.get("dram_gbs") else None,
+                               algorithmic_bytes_per_launch_ncu=tr.get("algorithmic_bytes_per_launch"),
+                               l1_hit=tr.get("l1_hit"), l2_hit=tr.get("l2_hit"), issue_active=tr.get("issue_active"), lanes_per_inst=tr.get("lanes_per_inst"),
+                               bound_by=tr.get("bound_by"),
                                peak_source="MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback",
-                               kernel="k_trace<0|1|2> (BVH traversal: extend, shadow, MIS rays)",
+                               kernel="k_trace<0|1|3> (BVH traversal: extend, shadow, MIS emitter rays)",
+                               byte_definition="80 B x nodes + 48 B x triangles fetched (SURVEY 8d); frac_112B uses the 112 B a node occupies",
                                method="algorithmic bytes per step / (traversal share x timed step); share from the serial event-pair pass",
                                trace_share=round(share, 4), achieved_serial_launches=round(ach_serial, 1),
                                serial_trace_ms_per_step=round(stt["ms_trace"], 3), serial_shade_ms_per_step=round(stt["ms_shade"], 3),
                                serial_step_ms=round(stt["ms_render"], 3), trace_launches_per_step=n_trace_launches,
                                avg_launch_us_serial=round(1e3 * stt["ms_trace"] / n_trace_launches, 1),
                                nodes_per_ray=round(sc["nodes_fetched"] / nrays, 2), tris_per_ray=round(sc["tris_fetched"] / nrays, 2),
-                               bytes_per_ray=round(algo / nrays, 1), bound_mrays=round(peak * 1e9 / (algo / nrays) / 1e6, 1),
+                               bytes_per_ray=round(algo / nrays, 1), bytes_per_ray_112B=round(algo112 / nrays, 1), bound_mrays=round(peak * 1e9 / (algo / nrays) / 1e6, 1),
                                max_nodes_one_ray=sc["max_nodes_per_ray"], max_tris_one_ray=sc["max_tris_per_ray"], bvh_depth=sc["bvh_depth"])
         if not args.no_cpu:
             vals, info = cpu_arm(scene, cfg, budget_s=args.cpu_budget)
@@ -300,7 +342,7 @@ def reference_arm(args, rank, world):
     vals, info = cpu_arm(scene, cfg, budget_s=args.cpu_budget, steps=args.steps, warmup=min(args.warmup, 1))
     v = float(np.mean(vals))
     out = dict(metric="Mrays/s", value=round(v, 3), unit="Mrays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
-               ms_per_step=round(1e3 * info["seconds"], 3), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
+               ms_per_step=round(1e3 * info["seconds"], 3), higher_is_better=True, scaling=args.scaling, vs_baseline=None, dtype="f32",
                data="synthetic", impl="reference",
                config=dict(workload=desc, triangles=scene.n_triangles, width=cfg["width"], height=cfg["height"], max_depth=cfg["max_depth"], integrator="MIS"),
                cpu_baseline=dict(value=round(v, 3), unit="Mrays/s", cores=info["cores"], kind=info["kind"], sample=info["sample"]),
@@ -320,6 +362,8 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--pageable", action="store_true", help="e2e leg with pageable host buffers (no hj_host_pin)")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="N > 1: split the fixed frame (strong, default) or 64 spp per rank (weak)")
+    ap.add_argument("--as-rank-of", type=int, default=1, help="one GPU: render rank 0's slice of an N-way strong split (predicts the split without the box)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
