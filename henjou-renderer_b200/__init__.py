@@ -9,3 +9,4 @@ from .camera import camera_basis, frame_params                # noqa: F401
 from .sceneio import save_npz, load_npz                       # noqa: F401
 from .renderer import Renderer, HenjouError, load_library, LIB_PATH   # noqa: F401
 from .slices import sample_slice, weak_slice   # noqa: F401
+from . import hdrio                  # noqa: F401

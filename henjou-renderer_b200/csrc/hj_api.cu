@@ -72,7 +72,7 @@ int hj_create(hj_ctx** out, int device) {
     c->device = device;
     if (const char* v = getenv("HJ_VERIFY_ACCEL")) c->opt_verify_accel = atoi(v) != 0;    // the test suite sets it
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess || (e = cudaEventCreate(&c->ev0)) != cudaSuccess ||
-        (e = cudaEventCreate(&c->ev1)) != cudaSuccess) {
+        (e = cudaEventCreate(&c->ev1)) != cudaSuccess || (e = cudaEventCreateWithFlags(&c->ev_scene, cudaEventDisableTiming)) != cudaSuccess) {
         g_create_err = cudaGetErrorString(e); delete c; return HJ_ERR_CUDA;
     }
     *out = c;
@@ -87,15 +87,16 @@ void hj_destroy(hj_ctx* c) {
     cudaStreamSynchronize(c->stream);
     hj_comm_destroy_internal(c);
     DevBuf* bufs[] = {&c->d_vertices, &c->d_normals, &c->d_texcoords, &c->d_indices, &c->d_material_ids, &c->d_prim_offsets, &c->d_tri_inst,
-                      &c->d_xf, &c->d_inv_xf, &c->d_materials, &c->d_textures, &c->d_texels, &c->d_srgb, &c->d_light_ids, &c->d_light_em,
-                      &c->d_ibl, &c->d_lut, &c->d_tri_pos, &c->d_tri_attr,
-                      &c->bvh.keys, &c->bvh.keys_alt, &c->bvh.vals, &c->bvh.vals_alt, &c->bvh.block_hist, &c->bvh.blo, &c->bvh.bhi, &c->bvh.left,
+                      &c->d_materials, &c->d_textures, &c->d_texels, &c->d_srgb, &c->d_light_ids, &c->d_light_em,
+                      &c->d_ibl, &c->d_lut,
+                      &c->bvh.keys, &c->bvh.keys_alt, &c->bvh.vals, &c->bvh.vals_alt, &c->bvh.block_hist, &c->bvh.digit_total, &c->bvh.status, &c->bvh.blo, &c->bvh.bhi, &c->bvh.left,
                       &c->bvh.right, &c->bvh.parent, &c->bvh.cnt, &c->bvh.flags, &c->bvh.p_cid[0], &c->bvh.p_cid[1], &c->bvh.p_lo[0], &c->bvh.p_lo[1],
                       &c->bvh.p_hi[0], &c->bvh.p_hi[1], &c->bvh.p_nn, &c->bvh.p_keep, &c->bvh.p_bcount, &c->bvh.bounds, &c->bvh.queue_a, &c->bvh.queue_b,
-                      &c->bvh.counters, &c->bvh.verr, &c->bvh.nodes, &c->bvh.btris,
+                      &c->bvh.counters, &c->bvh.verr,
                       &c->aov_color, &c->aov_albedo, &c->aov_normal, &c->aov_rgba8, &c->aov_accum, &c->aov_path_rad, &c->aov_path_ids,
                       &c->aov_output, &c->aov_output_rgba8, &c->post_tmp[0], &c->post_tmp[1]};
     for (DevBuf* b : bufs) b->release();
+    hj_bvh_release(c);
     for (WavefrontState& w : c->wf) {
         for (DevBuf* b : w.all) if (b) b->release();
         if (w.stream) cudaStreamDestroy(w.stream);
@@ -105,7 +106,7 @@ void hj_destroy(hj_ctx* c) {
     if (c->ev_post0) cudaEventDestroy(c->ev_post0);
     if (c->ev_post1) cudaEventDestroy(c->ev_post1);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
-    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev_scene);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -149,6 +150,8 @@ int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
     for (uint32_t i = 0; i < d->n_light_prims; i++)
         HJ_REQUIRE(c, d->light_prim_ids && d->light_prim_emission && d->light_prim_ids[i] < d->n_triangles, HJ_ERR_INVALID, "hj_scene_upload: bad light primitive list");
     HJ_CUDA(c, cudaSetDevice(c->device));
+    (void)hj_bvh_finish(c);                                  // a build in flight reads the arrays replaced below
+    HJ_CUDA(c, cudaStreamSynchronize(c->stream));
     c->have_scene = c->have_accel = c->have_frame = c->have_output = false;
     c->bvh.have_topology = false;
     int rc;
@@ -218,6 +221,7 @@ int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
     else if ((rc = upload(c, c->d_ibl, black, (size_t)4))) return rc;
     const bool has_lut = d->lut_rgba8 && d->lut_width > 0 && d->lut_height > 0;
     if (has_lut) { if ((rc = upload(c, c->d_lut, d->lut_rgba8, 4 * (size_t)d->lut_width * d->lut_height))) return rc; }
+    HJ_CUDA(c, cudaEventRecord(c->ev_scene, c->stream));
     HJ_CUDA(c, cudaStreamSynchronize(c->stream));
     DevScene& S = c->S;
     S = DevScene{};
@@ -234,52 +238,39 @@ int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
     return HJ_OK;
 }
 
-// General 3x4 affine inverse by cofactors in float (the reference uses glm::inverse on the 4x4, renderer.h:272-284)
-static void invert_affine(const float* m, float* r) {
-    const float a = m[0], b = m[1], cc = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
-    const float A = e * i - f * h, B = -(d * i - f * g), C = d * h - e * g;
-    const float det = a * A + b * B + cc * C;
-    const float id = 1.0f / det;
-    r[0] = A * id; r[1] = -(b * i - cc * h) * id; r[2] = (b * f - cc * e) * id;
-    r[4] = B * id; r[5] = (a * i - cc * g) * id; r[6] = -(a * f - cc * d) * id;
-    r[8] = C * id; r[9] = -(a * h - b * g) * id; r[10] = (a * e - b * d) * id;
-    const float tx = m[3], ty = m[7], tz = m[11];
-    r[3] = -(r[0] * tx + r[1] * ty + r[2] * tz);
-    r[7] = -(r[4] * tx + r[5] * ty + r[6] * tz);
-    r[11] = -(r[8] * tx + r[9] * ty + r[10] * tz);
+static int accel_args_ok(hj_ctx* c, uint32_t n_instances, int mode, const char* who) {
+    HJ_REQUIRE(c, c->have_scene, HJ_ERR_NO_SCENE, std::string(who) + ": no scene uploaded");
+    HJ_REQUIRE(c, n_instances == c->S.n_instances, HJ_ERR_INVALID, std::string(who) + ": n_instances differs from the uploaded scene");
+    HJ_REQUIRE(c, mode == HJ_ACCEL_BUILD || mode == HJ_ACCEL_REFIT, HJ_ERR_INVALID, std::string(who) + ": unknown mode");
+    return HJ_OK;
+}
+
+int hj_accel_build_async(hj_ctx* c, const float* xf, const float* inv_xf, uint32_t n_instances, int mode) {
+    if (!c) return HJ_ERR_INVALID;
+    int rc = accel_args_ok(c, n_instances, mode, "hj_accel_build_async");
+    if (rc) return rc;
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    if ((rc = hj_bvh_finish(c))) return rc;               // at most one build in flight
+    return hj_bvh_enqueue(c, xf, inv_xf, mode);
+}
+
+int hj_accel_wait(hj_ctx* c) {
+    if (!c) return HJ_ERR_INVALID;
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    return hj_bvh_finish(c);
 }
 
 int hj_accel_build(hj_ctx* c, const float* xf, const float* inv_xf, uint32_t n_instances, int mode) {
-    if (!c) return HJ_ERR_INVALID;
-    HJ_REQUIRE(c, c->have_scene, HJ_ERR_NO_SCENE, "hj_accel_build: no scene uploaded");
-    HJ_REQUIRE(c, n_instances == c->S.n_instances, HJ_ERR_INVALID, "hj_accel_build: n_instances differs from the uploaded scene");
-    HJ_REQUIRE(c, mode == HJ_ACCEL_BUILD || mode == HJ_ACCEL_REFIT, HJ_ERR_INVALID, "hj_accel_build: unknown mode");
-    HJ_CUDA(c, cudaSetDevice(c->device));
-    std::vector<float> m(12 * (size_t)n_instances), im(12 * (size_t)n_instances);
-    for (uint32_t i = 0; i < n_instances; i++) {
-        float* p = &m[12 * (size_t)i]; float* q = &im[12 * (size_t)i];
-        if (xf) memcpy(p, xf + 12 * (size_t)i, 48);
-        else { memset(p, 0, 48); p[0] = p[5] = p[10] = 1.0f; }
-        if (inv_xf) memcpy(q, inv_xf + 12 * (size_t)i, 48);
-        else if (xf) invert_affine(p, q);
-        else memcpy(q, p, 48);
-    }
-    int rc;
-    if ((rc = upload(c, c->d_xf, m.data(), m.size()))) return rc;
-    if ((rc = upload(c, c->d_inv_xf, im.data(), im.size()))) return rc;
-    HJ_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->S.xf = c->d_xf.as<float4>(); c->S.inv_xf = c->d_inv_xf.as<float4>();
-    c->have_accel = false;
-    if ((rc = hj_bvh_build(c, mode))) return rc;
-    c->have_accel = true;
-    return HJ_OK;
+    int rc = hj_accel_build_async(c, xf, inv_xf, n_instances, mode);
+    return rc ? rc : hj_bvh_finish(c);
 }
 
 int hj_render_async(hj_ctx* c, const hj_frame_params* fp) {
     if (!c || !fp) return HJ_ERR_INVALID;
     HJ_REQUIRE(c, c->have_scene, HJ_ERR_NO_SCENE, "hj_render: no scene uploaded");
-    HJ_REQUIRE(c, c->have_accel, HJ_ERR_NO_ACCEL, "hj_render: hj_accel_build has not been called");
     HJ_CUDA(c, cudaSetDevice(c->device));
+    { int rc = hj_bvh_finish(c); if (rc) return rc; }     // a build enqueued by hj_accel_build_async: validate it and flip to its buffers
+    HJ_REQUIRE(c, c->have_accel, HJ_ERR_NO_ACCEL, "hj_render: hj_accel_build has not been called");
     return hj_wavefront_render(c, fp);
 }
 
@@ -390,8 +381,9 @@ int hj_get_stats(hj_ctx* c, hj_stats* out) {
 
 int hj_trace(hj_ctx* c, const float* rays, uint64_t n, int any_hit, uint32_t* prim, float* tuv) {
     if (!c || (n && !rays)) return HJ_ERR_INVALID;
-    HJ_REQUIRE(c, c->have_accel, HJ_ERR_NO_ACCEL, "hj_trace: hj_accel_build has not been called");
     HJ_CUDA(c, cudaSetDevice(c->device));
+    { int rc = hj_bvh_finish(c); if (rc) return rc; }
+    HJ_REQUIRE(c, c->have_accel, HJ_ERR_NO_ACCEL, "hj_trace: hj_accel_build has not been called");
     return hj_trace_batch(c, rays, n, any_hit, prim, tuv);
 }
 

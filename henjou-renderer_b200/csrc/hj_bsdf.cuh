@@ -37,7 +37,8 @@ struct Disney {
         float phi = 2.0f * HJ_PI * uv.x;
         float z = fmaf((1.0f - uv.y), (1.0f + swo.y), -swo.y);
         float st = sqrtf(clampf(1.0f - z * z, 0.0f, 1.0f));
-        float x = st * hj_cosf(phi), y = st * hj_sinf(phi);
+        float sp, cp; hj_sincosf(phi, sp, cp);        // one range reduction for both: same bits as cosf(phi), sinf(phi)
+        float x = st * cp, y = st * sp;
         float3 h = f3(x, z, y) + swo;
         return normalize(f3(h.x * alpha, h.y, h.z * alpha));
     }
@@ -60,7 +61,8 @@ struct Disney {
         float ct = sqrtf(fmaxf((1.0f - hj_powf(cc_alpha * cc_alpha, 1.0f - uv.x)) / (1.0f - cc_alpha * cc_alpha), 0.0f));
         float st = sqrtf(fmaxf(1.0f - ct * ct, 0.0f));
         float phi = HJ_TWO_PI * uv.y;
-        float3 wm = f3(hj_cosf(phi) * st, ct, hj_sinf(phi) * st);
+        float sp, cp; hj_sincosf(phi, sp, cp);
+        float3 wm = f3(cp * st, ct, sp * st);
         pdf = pdf_clearcoat(wm, wo);
         return wm;
     }
@@ -115,8 +117,8 @@ struct Disney {
         if (sel < dw) {
             float theta = 0.5f * hj_acosf(1.0f - 2.0f * xi.x);    // sampleDiffuse :30-38
             float phi = 2.0f * M_PIf * xi.y;
-            float ct = hj_cosf(theta), sn = hj_sinf(theta);
-            wi = f3(hj_cosf(phi) * sn, ct, hj_sinf(phi) * sn);
+            float ct, sn, cp, sp; hj_sincosf(theta, sn, ct); hj_sincosf(phi, sp, cp);
+            wi = f3(cp * sn, ct, sp * sn);
             pd = pdf_diffuse(wi);
             float3 wm = normalize(wi + wo);
             ps = pdf_specular(wm, wo);
@@ -204,7 +206,8 @@ struct MultiScatterGGX {
         float phi = 2.0f * HJ_PI * uv.x;
         float z = fmaf((1.0f - uv.y), (1.0f + swo.y), -swo.y);
         float st = sqrtf(clampf(1.0f - z * z, 0.0f, 1.0f));
-        float x = st * hj_cosf(phi), y = st * hj_sinf(phi);
+        float sp, cp; hj_sincosf(phi, sp, cp);        // one range reduction for both: same bits as cosf(phi), sinf(phi)
+        float x = st * cp, y = st * sp;
         float3 h = f3(x, z, y) + swo;
         return normalize(f3(h.x * alpha, h.y, h.z * alpha));
     }

@@ -11,6 +11,17 @@
 //   k_collapse     level-by-level collapse to 8-wide nodes with 8-bit quantised child boxes (112 B / node)
 #include "hj_ctx.h"
 #include "hj_trace.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+
+// results of a build, written by the device, mirrored into pinned host memory at the end of the enqueued work
+struct BuildStatus {
+    uint32_t n_nodes, n_tris, depth, error;        // error bits: HJ_BUILD_ERR_*
+    uint32_t cur_n, node_ctr, pp, ploc_rounds;     // PLOC hand-over from the cooperative kernel to the tail
+};
+#define HJ_BUILD_ERR_NONFINITE 1u      // a world-space vertex is NaN / inf
+#define HJ_BUILD_ERR_PLOC 2u           // a PLOC round merged nothing (only with non-finite boxes)
+#define HJ_BUILD_ERR_COLLAPSE 4u       // the collapse did not terminate within the level bound
 
 #define RS_THREADS 256
 #define RS_ITEMS 16
@@ -21,14 +32,9 @@
 HJ_DI int f2ord(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
 HJ_DI float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
-__global__ void k_init_bounds(int* b) {
-    if (threadIdx.x < 3) b[threadIdx.x] = 0x7fffffff;
-    else if (threadIdx.x < 6) b[threadIdx.x] = (int)0x80000000;
-}
-
 // ≙ the vertex fetch + transform of __closesthit__ch (stale PTX :880-1287) hoisted out of the hit program:
 // p_k = transform_position(transforms[inst], vertices[i_k]); n_k = normalize(transform_normal(inv[inst], normals[i_k]))
-__global__ void k_flatten(DevScene S, int* bounds) {
+__global__ void k_flatten(DevScene S, int* bounds, uint32_t* error) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     if (t < S.n_tris) {
@@ -40,6 +46,7 @@ __global__ void k_flatten(DevScene S, int* bounds) {
             p[k] = xform_point(m, ld3(S.vertices, vi));
             n[k] = normalize(xform_normal(im, ld3(S.normals, vi)));
             uv[k] = make_float2(S.texcoords[2 * (size_t)vi], S.texcoords[2 * (size_t)vi + 1]);
+            if (!(fabsf(p[k].x) <= FLT_MAX && fabsf(p[k].y) <= FLT_MAX && fabsf(p[k].z) <= FLT_MAX)) atomicOr(error, HJ_BUILD_ERR_NONFINITE);   // a NaN box can never merge
             lo[0] = fminf(lo[0], p[k].x); lo[1] = fminf(lo[1], p[k].y); lo[2] = fminf(lo[2], p[k].z);
             hi[0] = fmaxf(hi[0], p[k].x); hi[1] = fmaxf(hi[1], p[k].y); hi[2] = fmaxf(hi[2], p[k].z);
         }
@@ -101,16 +108,19 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const uint64_t* __restri
     block_hist[threadIdx.x * nb + blockIdx.x] = h[threadIdx.x];
 }
 
-// exclusive scan of `len` counters in place, one block
-__global__ void __launch_bounds__(1024) k_rs_scan(uint32_t* a, uint32_t len) {
-    __shared__ uint32_t part[1024];
-    const uint32_t per = (len + 1023u) / 1024u;
-    const uint32_t b = min(threadIdx.x * per, len), e = min(b + per, len);
+// block_hist is [digit][tile]. One block per digit scans its row in place (exclusive) and writes the digit's total; the scatter
+// kernel adds the exclusive scan of the 256 totals itself. (Round 1 scanned all 256 x tiles counters in ONE block.)
+#define RS_SCAN_THREADS 256
+__global__ void __launch_bounds__(RS_SCAN_THREADS) k_rs_scan_rows(uint32_t* hist, uint32_t nb, uint32_t* digit_total) {
+    __shared__ uint32_t part[RS_SCAN_THREADS];
+    uint32_t* a = hist + (size_t)blockIdx.x * nb;
+    const uint32_t per = (nb + RS_SCAN_THREADS - 1) / RS_SCAN_THREADS;
+    const uint32_t b = min(threadIdx.x * per, nb), e = min(b + per, nb);
     uint32_t s = 0;
     for (uint32_t i = b; i < e; i++) s += a[i];
     part[threadIdx.x] = s;
     __syncthreads();
-    for (int o = 1; o < 1024; o <<= 1) {
+    for (int o = 1; o < RS_SCAN_THREADS; o <<= 1) {
         uint32_t v = (threadIdx.x >= (uint32_t)o) ? part[threadIdx.x - o] : 0u;
         __syncthreads();
         part[threadIdx.x] += v;
@@ -118,13 +128,26 @@ __global__ void __launch_bounds__(1024) k_rs_scan(uint32_t* a, uint32_t len) {
     }
     uint32_t run = part[threadIdx.x] - s;
     for (uint32_t i = b; i < e; i++) { uint32_t v = a[i]; a[i] = run; run += v; }
+    if (threadIdx.x == RS_SCAN_THREADS - 1) digit_total[blockIdx.x] = part[RS_SCAN_THREADS - 1];
 }
 
 __global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, uint32_t n, int shift,
-                                                           const uint32_t* __restrict__ block_off, uint32_t nb,
+                                                           const uint32_t* __restrict__ block_off, const uint32_t* __restrict__ digit_total, uint32_t nb,
                                                            uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
     __shared__ uint32_t wh[RS_THREADS / 32][256];
+    __shared__ uint32_t dbase[256];
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    {   // exclusive scan of the 256 digit totals (first write position of every digit)
+        const uint32_t t = digit_total[threadIdx.x];
+        uint32_t incl = t;
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+        __shared__ uint32_t wsum[RS_THREADS / 32];
+        if (lane == 31) wsum[w] = incl;
+        __syncthreads();
+        uint32_t off = 0;
+        for (int ww = 0; ww < w; ww++) off += wsum[ww];
+        dbase[threadIdx.x] = off + incl - t;
+    }
     for (int i = threadIdx.x; i < (RS_THREADS / 32) * 256; i += RS_THREADS) (&wh[0][0])[i] = 0;
     __syncthreads();
     const uint32_t base = blockIdx.x * RS_TILE + w * (32 * RS_ITEMS);
@@ -147,7 +170,7 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const uint64_t* __res
     __syncthreads();
     {   // digit = threadIdx.x: turn per-warp counts into global write offsets
         const int d = threadIdx.x;
-        uint32_t run = block_off[d * nb + blockIdx.x];
+        uint32_t run = dbase[d] + block_off[d * nb + blockIdx.x];
         for (int ww = 0; ww < RS_THREADS / 32; ww++) { uint32_t c = wh[ww][d]; wh[ww][d] = run; run += c; }
     }
     __syncthreads();
@@ -235,10 +258,18 @@ __global__ void k_fit(const DevScene S, const uint32_t* __restrict__ sorted, int
 // clusters. Every round each cluster looks PLOC_RADIUS neighbours to either side for the partner that minimises the
 // surface area of the merged box; mutual nearest neighbours merge. Builds a much better tree than the Karras radix
 // tree over the same order (fewer node visits per ray, no pathological long rays through flat tessellated surfaces).
+//
+// r02: the whole agglomeration is ONE cooperative kernel (grid-wide barriers between the phases of a round) followed by a
+// single-block tail for the last <= 1024 clusters. Round 1 ran every round as four launches and read the cluster count back
+// to the host after each (one cudaStreamSynchronize per round, ~20 rounds): that made hj_accel_build a blocking call and
+// kept it from running under the previous frame's shading. Internal node ids are now assigned by prefix
+// sums instead of a global atomic, so the same input gives the same tree layout in every run.
 #ifndef PLOC_RADIUS
 #define PLOC_RADIUS 8      // r01-u sweep on C2 (2..100): 6-8 give the fewest node visits and the shortest build
 #endif
 #define PLOC_THREADS 256
+#define PLOC_TAIL 1024
+
 
 __global__ void k_ploc_init(const DevScene S, const uint32_t* __restrict__ sorted, int n, uint32_t* cid, float4* clo, float4* chi, float4* blo, float4* bhi) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -257,14 +288,12 @@ HJ_DI float merged_area(const float4& alo, const float4& ahi, const float4& blo,
     return dx * dy + dy * dz + dz * dx;
 }
 
-// nearest neighbour inside the window; ties resolved by the (min index, max index) pair so that "nearest" is a strict
-// total order on pairs and the globally closest pair is always mutual (guarantees progress)
-__global__ void __launch_bounds__(PLOC_THREADS) k_ploc_nn(int n, const float4* __restrict__ clo, const float4* __restrict__ chi, uint32_t* __restrict__ nn) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+// nearest neighbour of cluster i inside the window; ties resolved by the (min index, max index) pair so that "nearest" is a
+// strict total order on pairs and the globally closest pair is always mutual (guarantees progress on finite boxes)
+HJ_DI int ploc_nearest(int i, int cur, const float4* clo, const float4* chi) {   // no __restrict__: other blocks wrote these arrays in the previous round (no ld.global.nc)
     const float4 lo = clo[i], hi = chi[i];
     float best = FLT_MAX; int bj = -1;
-    const int j0 = max(0, i - PLOC_RADIUS), j1 = min(n - 1, i + PLOC_RADIUS);
+    const int j0 = max(0, i - PLOC_RADIUS), j1 = min(cur - 1, i + PLOC_RADIUS);
     for (int j = j0; j <= j1; j++) {
         if (j == i) continue;
         const float d = merged_area(lo, hi, clo[j], chi[j]);
@@ -275,120 +304,149 @@ __global__ void __launch_bounds__(PLOC_THREADS) k_ploc_nn(int n, const float4* _
         }
         if (better) { best = d; bj = j; }
     }
-    nn[i] = (uint32_t)bj;
+    return bj;
 }
 
-__global__ void __launch_bounds__(PLOC_THREADS) k_ploc_merge(int n, int n_leaves, uint32_t* cid, float4* clo, float4* chi, const uint32_t* __restrict__ nn,
-                                                               uint32_t* node_ctr, uint32_t* left, uint32_t* right, uint32_t* parent, uint32_t* cnt,
-                                                               float4* blo, float4* bhi, uint32_t* keep, uint32_t* block_count) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    int k = 0;
-    if (i < n) {
-        const int j = (int)nn[i];
-        const bool mutual = j >= 0 && (int)nn[j] == i;
-        k = 1;
-        if (mutual) {
-            if (i < j) {
-                const uint32_t id = atomicAdd(node_ctr, 1u);
-                const uint32_t a = cid[i], b = cid[j];
-                const float4 alo = clo[i], ahi = chi[i], xlo = clo[j], xhi = chi[j];
-                const float4 lo = make_float4(fminf(alo.x, xlo.x), fminf(alo.y, xlo.y), fminf(alo.z, xlo.z), fmaxf(alo.w, xlo.w));
-                const float4 hi = make_float4(fmaxf(ahi.x, xhi.x), fmaxf(ahi.y, xhi.y), fmaxf(ahi.z, xhi.z), 0.0f);
-                left[id] = a; right[id] = b; parent[a] = id; parent[b] = id;
-                cnt[id] = (a >= (uint32_t)(n_leaves - 1) ? 1u : cnt[a]) + (b >= (uint32_t)(n_leaves - 1) ? 1u : cnt[b]);
-                blo[id] = lo; bhi[id] = hi;
-                cid[i] = id; clo[i] = lo; chi[i] = hi;
-            } else k = 0;
-        }
-        keep[i] = (uint32_t)k;
-    }
-    const int total = __syncthreads_count(k);
-    if (threadIdx.x == 0) block_count[blockIdx.x] = (uint32_t)total;
+struct PlocArgs {
+    int n, tail_at;
+    uint32_t* cid[2]; float4* clo[2]; float4* chi[2];
+    int* nn; uint32_t *bkeep, *bmerge;             // per-block keep / merge counts of the current round
+    uint32_t *left, *right, *parent, *cnt; float4 *blo, *bhi;
+    BuildStatus* st;
+};
+
+// the merge of clusters (a, b) into the new internal node `id`
+HJ_DI void ploc_make_node(const PlocArgs& A, uint32_t id, uint32_t a, uint32_t b, const float4& alo, const float4& ahi, const float4& xlo, const float4& xhi,
+                          float4& lo, float4& hi) {
+    lo = make_float4(fminf(alo.x, xlo.x), fminf(alo.y, xlo.y), fminf(alo.z, xlo.z), fmaxf(alo.w, xlo.w));
+    hi = make_float4(fmaxf(ahi.x, xhi.x), fmaxf(ahi.y, xhi.y), fmaxf(ahi.z, xhi.z), 0.0f);
+    const uint32_t first_leaf = (uint32_t)(A.n - 1);
+    A.left[id] = a; A.right[id] = b; A.parent[a] = id; A.parent[b] = id;
+    A.cnt[id] = (a >= first_leaf ? 1u : A.cnt[a]) + (b >= first_leaf ? 1u : A.cnt[b]);
+    A.blo[id] = lo; A.bhi[id] = hi;
 }
 
-__global__ void __launch_bounds__(PLOC_THREADS) k_ploc_compact(int n, const uint32_t* __restrict__ keep, const uint32_t* __restrict__ block_off,
-                                                                 const uint32_t* __restrict__ cid, const float4* __restrict__ clo, const float4* __restrict__ chi,
-                                                                 uint32_t* __restrict__ cid2, float4* __restrict__ clo2, float4* __restrict__ chi2) {
-    __shared__ uint32_t wsum[PLOC_THREADS / 32];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool k = i < n && keep[i] != 0u;
-    const uint32_t m = __ballot_sync(0xffffffffu, k);
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (lane == 0) wsum[w] = __popc(m);
+// block-wide sum of two counters (every thread gets both totals)
+HJ_DI void block_sum2(uint32_t& x, uint32_t& y, uint32_t* s /* [2 * warps + 2] */) {
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const uint32_t sx = __reduce_add_sync(0xffffffffu, x), sy = __reduce_add_sync(0xffffffffu, y);
     __syncthreads();
-    uint32_t base = block_off[blockIdx.x];
-    for (int ww = 0; ww < w; ww++) base += wsum[ww];
-    if (k) {
-        const uint32_t pos = base + __popc(m & ((1u << lane) - 1u));
-        cid2[pos] = cid[i]; clo2[pos] = clo[i]; chi2[pos] = chi[i];
+    if (lane == 0) { s[w] = sx; s[nw + w] = sy; }
+    __syncthreads();
+    uint32_t tx = 0, ty = 0;
+    for (int k = 0; k < nw; k++) { tx += s[k]; ty += s[nw + k]; }
+    x = tx; y = ty;
+}
+
+// Every block owns a contiguous chunk of the cluster array, so a stable compaction needs only the counts of the blocks before it.
+__global__ void __launch_bounds__(PLOC_THREADS) k_ploc_coop(PlocArgs A) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ uint32_t s_red[2 * (PLOC_THREADS / 32) + 2];
+    __shared__ uint32_t s_wk[PLOC_THREADS / 32], s_wm[PLOC_THREADS / 32];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, w = tid >> 5;
+    const uint32_t gtid = blockIdx.x * PLOC_THREADS + tid, gsize = gridDim.x * PLOC_THREADS;
+    uint32_t cur = (uint32_t)A.n, node_base = 0, rounds = 0, err = 0; int pp = 0;
+    while (cur > (uint32_t)A.tail_at && cur > 1u) {
+        const float4* clo = A.clo[pp]; const float4* chi = A.chi[pp]; const uint32_t* cid = A.cid[pp];
+        for (uint32_t i = gtid; i < cur; i += gsize) A.nn[i] = ploc_nearest((int)i, (int)cur, clo, chi);
+        grid.sync();
+        uint32_t chunk = (cur + gridDim.x - 1) / gridDim.x;
+        chunk = (chunk + PLOC_THREADS - 1) / PLOC_THREADS * PLOC_THREADS;
+        const uint32_t c0 = min(blockIdx.x * chunk, cur), c1 = min(c0 + chunk, cur);
+        uint32_t nk = 0, nm = 0;                          // clusters this block keeps / merges it leads
+        for (uint32_t i = c0 + tid; i < c1; i += PLOC_THREADS) {
+            const int j = A.nn[i];
+            const bool mutual = j >= 0 && A.nn[j] == (int)i;
+            nk += (mutual && (int)i > j) ? 0u : 1u; nm += (mutual && (int)i < j) ? 1u : 0u;
+        }
+        block_sum2(nk, nm, s_red);
+        if (tid == 0) { A.bkeep[blockIdx.x] = nk; A.bmerge[blockIdx.x] = nm; }
+        grid.sync();
+        uint32_t koff = 0, moff = 0, ktot = 0, mtot = 0;  // counts of the blocks before this one, and of all blocks
+        for (uint32_t b = tid; b < gridDim.x; b += PLOC_THREADS) {
+            const uint32_t k = A.bkeep[b], m = A.bmerge[b];
+            ktot += k; mtot += m; if (b < blockIdx.x) { koff += k; moff += m; }
+        }
+        block_sum2(ktot, mtot, s_red); block_sum2(koff, moff, s_red);
+        uint32_t* cid2 = A.cid[pp ^ 1]; float4* clo2 = A.clo[pp ^ 1]; float4* chi2 = A.chi[pp ^ 1];
+        for (uint32_t t0 = c0; t0 < c1; t0 += PLOC_THREADS) {
+            const uint32_t i = t0 + tid;
+            bool keep = false, lead = false; int j = -1;
+            if (i < c1) { j = A.nn[i]; const bool mutual = j >= 0 && A.nn[j] == (int)i; keep = !(mutual && (int)i > j); lead = mutual && (int)i < j; }
+            const uint32_t mk = __ballot_sync(0xffffffffu, keep), mm = __ballot_sync(0xffffffffu, lead);
+            __syncthreads();
+            if (lane == 0) { s_wk[w] = __popc(mk); s_wm[w] = __popc(mm); }
+            __syncthreads();
+            uint32_t bk = 0, bm = 0, tk = 0, tm = 0;
+            for (uint32_t ww = 0; ww < PLOC_THREADS / 32; ww++) { if (ww < w) { bk += s_wk[ww]; bm += s_wm[ww]; } tk += s_wk[ww]; tm += s_wm[ww]; }
+            if (keep) {
+                const uint32_t pos = koff + bk + __popc(mk & ((1u << lane) - 1u));
+                uint32_t id = cid[i]; float4 lo = clo[i], hi = chi[i];
+                if (lead) {
+                    const uint32_t nid = node_base + moff + bm + __popc(mm & ((1u << lane) - 1u));
+                    ploc_make_node(A, nid, id, cid[j], lo, hi, clo[j], chi[j], lo, hi);
+                    id = nid;
+                }
+                cid2[pos] = id; clo2[pos] = lo; chi2[pos] = hi;
+            }
+            koff += tk; moff += tm;
+        }
+        if (mtot == 0u) { err = HJ_BUILD_ERR_PLOC; break; }      // uniform over the grid: no pair was mutual (non-finite boxes)
+        cur = ktot; node_base += mtot; pp ^= 1; rounds++;
+        grid.sync();
+    }
+    if (grid.thread_rank() == 0) {
+        A.st->cur_n = cur; A.st->node_ctr = node_base; A.st->pp = (uint32_t)pp; A.st->ploc_rounds = rounds;
+        if (err) atomicOr(&A.st->error, err);
     }
 }
 
-// The last rounds of PLOC work on a handful of clusters and are pure launch + host-synchronisation latency (C2: 67 rounds,
-// ~50 of them on fewer than 1024 clusters, ~45 us each). Once the clusters fit one block, this kernel runs the remaining
-// rounds in shared memory: the same nearest-neighbour rule, merges and compaction as k_ploc_nn / k_ploc_merge /
-// k_ploc_compact, so the tree is the same.
-#define PLOC_TAIL 1024
-__global__ void __launch_bounds__(PLOC_TAIL) k_ploc_tail(int n, int n_leaves, const uint32_t* __restrict__ cid_in, const float4* __restrict__ clo_in,
-                                                          const float4* __restrict__ chi_in, uint32_t* node_ctr, uint32_t* left, uint32_t* right, uint32_t* parent,
-                                                          uint32_t* cnt, float4* blo, float4* bhi) {
+// The last rounds of PLOC work on a handful of clusters: once they fit one block they run in shared memory, same rules, same
+// prefix-sum node ids. Also sets the root's parent link. Launched unconditionally after k_ploc_coop; reads its state from *st.
+__global__ void __launch_bounds__(PLOC_TAIL) k_ploc_tail(PlocArgs A) {
     __shared__ float4 s_lo[PLOC_TAIL], s_hi[PLOC_TAIL];
     __shared__ uint32_t s_cid[PLOC_TAIL];
     __shared__ int s_nn[PLOC_TAIL];
-    __shared__ uint32_t s_wsum[PLOC_TAIL / 32];
+    __shared__ uint32_t s_wk[PLOC_TAIL / 32], s_wm[PLOC_TAIL / 32];
     const int i = threadIdx.x, w = i >> 5, lane = i & 31;
-    if (i < n) { s_cid[i] = cid_in[i]; s_lo[i] = clo_in[i]; s_hi[i] = chi_in[i]; }
+    if (A.st->error) return;
+    int cur = (int)A.st->cur_n; const int pp = (int)A.st->pp; uint32_t node_base = A.st->node_ctr, rounds = 0;
+    if (cur > PLOC_TAIL) return;                         // (ploc_tail off and more than one cluster left cannot happen: the loop above runs to 1)
+    if (i < cur) { s_cid[i] = A.cid[pp][i]; s_lo[i] = A.clo[pp][i]; s_hi[i] = A.chi[pp][i]; }
     __syncthreads();
-    int cur = n;
     while (cur > 1) {
-        if (i < cur) {                                   // k_ploc_nn
-            const float4 lo = s_lo[i], hi = s_hi[i];
-            float best = FLT_MAX; int bj = -1;
-            const int j0 = max(0, i - PLOC_RADIUS), j1 = min(cur - 1, i + PLOC_RADIUS);
-            for (int j = j0; j <= j1; j++) {
-                if (j == i) continue;
-                const float d = merged_area(lo, hi, s_lo[j], s_hi[j]);
-                bool better = d < best;
-                if (d == best && bj >= 0) {
-                    const int a0 = min(i, j), a1 = max(i, j), b0 = min(i, bj), b1 = max(i, bj);
-                    better = a0 < b0 || (a0 == b0 && a1 < b1);
-                }
-                if (better) { best = d; bj = j; }
-            }
-            s_nn[i] = bj;
-        }
+        if (i < cur) s_nn[i] = ploc_nearest(i, cur, s_lo, s_hi);
         __syncthreads();
-        bool keep = false;                               // k_ploc_merge
-        uint32_t my_cid = 0; float4 my_lo = make_float4(0, 0, 0, 0), my_hi = my_lo;
+        bool keep = false, lead = false;
+        uint32_t my_cid = 0, other = 0; float4 my_lo = make_float4(0, 0, 0, 0), my_hi = my_lo, xlo = my_lo, xhi = my_lo;
         if (i < cur) {
             const int j = s_nn[i];
             const bool mutual = j >= 0 && s_nn[j] == i;
-            keep = true; my_cid = s_cid[i]; my_lo = s_lo[i]; my_hi = s_hi[i];
-            if (mutual) {
-                if (i < j) {
-                    const uint32_t id = atomicAdd(node_ctr, 1u);
-                    const uint32_t a = my_cid, b = s_cid[j];
-                    const float4 xlo = s_lo[j], xhi = s_hi[j];
-                    const float4 lo = make_float4(fminf(my_lo.x, xlo.x), fminf(my_lo.y, xlo.y), fminf(my_lo.z, xlo.z), fmaxf(my_lo.w, xlo.w));
-                    const float4 hi = make_float4(fmaxf(my_hi.x, xhi.x), fmaxf(my_hi.y, xhi.y), fmaxf(my_hi.z, xhi.z), 0.0f);
-                    left[id] = a; right[id] = b; parent[a] = id; parent[b] = id;
-                    cnt[id] = (a >= (uint32_t)(n_leaves - 1) ? 1u : cnt[a]) + (b >= (uint32_t)(n_leaves - 1) ? 1u : cnt[b]);
-                    blo[id] = lo; bhi[id] = hi;
-                    my_cid = id; my_lo = lo; my_hi = hi;
-                } else keep = false;
-            }
+            keep = !(mutual && i > j); lead = mutual && i < j;
+            my_cid = s_cid[i]; my_lo = s_lo[i]; my_hi = s_hi[i];
+            if (lead) { other = s_cid[j]; xlo = s_lo[j]; xhi = s_hi[j]; }
         }
-        const uint32_t m = __ballot_sync(0xffffffffu, keep);      // k_ploc_compact (stable)
-        if (lane == 0) s_wsum[w] = (uint32_t)__popc(m);
+        const uint32_t mk = __ballot_sync(0xffffffffu, keep), mm = __ballot_sync(0xffffffffu, lead);
+        if (lane == 0) { s_wk[w] = (uint32_t)__popc(mk); s_wm[w] = (uint32_t)__popc(mm); }
         __syncthreads();                                 // also: every read of s_* of this round is done
-        uint32_t base = 0, total = 0;
-        for (int ww = 0; ww < PLOC_TAIL / 32; ww++) { const uint32_t v = s_wsum[ww]; if (ww < w) base += v; total += v; }
+        uint32_t bk = 0, bm = 0, tk = 0, tm = 0;
+        for (int ww = 0; ww < PLOC_TAIL / 32; ww++) { if (ww < w) { bk += s_wk[ww]; bm += s_wm[ww]; } tk += s_wk[ww]; tm += s_wm[ww]; }
         if (keep) {
-            const uint32_t pos = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+            if (lead) {
+                const uint32_t nid = node_base + bm + (uint32_t)__popc(mm & ((1u << lane) - 1u));
+                ploc_make_node(A, nid, my_cid, other, my_lo, my_hi, xlo, xhi, my_lo, my_hi);
+                my_cid = nid;
+            }
+            const uint32_t pos = bk + (uint32_t)__popc(mk & ((1u << lane) - 1u));
             s_cid[pos] = my_cid; s_lo[pos] = my_lo; s_hi[pos] = my_hi;
         }
         __syncthreads();
-        cur = (int)total;
+        if (tm == 0u) { if (i == 0) atomicOr(&A.st->error, HJ_BUILD_ERR_PLOC); return; }     // no mutual pair: non-finite boxes; never spin
+        cur = (int)tk; node_base += tm; rounds++;
+    }
+    if (i == 0) {
+        A.parent[A.n - 2] = 0xffffffffu;                 // ids are handed out in order: the last merge made the root
+        A.st->cur_n = 1u; A.st->node_ctr = node_base; A.st->ploc_rounds += rounds;
     }
 }
 
@@ -455,13 +513,14 @@ HJ_DI uint32_t grid_ceil(float chi, float lo, float scale) {
 // source change made nvcc 12.9 produce a kernel whose child boxes were overwritten while still live (children's
 // quantised boxes no longer contained their triangles -> missed hits). k_verify (option verify_accel) checks the result.
 #define COLLAPSE_THREADS 128
-__global__ void __launch_bounds__(COLLAPSE_THREADS) k_collapse(CollapseArgs a, const uint2* __restrict__ qin, uint32_t n_in, uint2* __restrict__ qout) {
-    __shared__ uint32_t s_ch[8][COLLAPSE_THREADS];
-    __shared__ float s_lo[3][8][COLLAPSE_THREADS], s_hi[3][8][COLLAPSE_THREADS];
+struct CollapseShared {
+    uint32_t ch[8][COLLAPSE_THREADS];
+    float lo[3][8][COLLAPSE_THREADS], hi[3][8][COLLAPSE_THREADS];
+};
+HJ_DI void collapse_one(const CollapseArgs& a, const uint2 work, uint2* __restrict__ qout, uint32_t* qlen_out, CollapseShared& sh) {
+    uint32_t (&s_ch)[8][COLLAPSE_THREADS] = sh.ch;
+    float (&s_lo)[3][8][COLLAPSE_THREADS] = sh.lo; float (&s_hi)[3][8][COLLAPSE_THREADS] = sh.hi;
     const uint32_t tid = threadIdx.x;
-    const uint32_t i = blockIdx.x * blockDim.x + tid;
-    if (i >= n_in) return;
-    const uint2 work = qin[i];
     const uint32_t first_leaf = (uint32_t)(a.n - 1);
     // Phase 0 opens the child with the largest surface area among those holding more than leaf_max triangles. Phase 1
     // (leaf_split): slots left over -> split multi-triangle leaf children too, largest box first: the node test looks at
@@ -565,7 +624,7 @@ __global__ void __launch_bounds__(COLLAPSE_THREADS) k_collapse(CollapseArgs a, c
     N[4] = make_uint4((uint32_t)qhy, (uint32_t)(qhy >> 32), (uint32_t)qhz, (uint32_t)(qhz >> 32));
     Nw[26] = em_word; Nw[27] = 0u;
     // children: queue the internal ones (contiguous, in slot order), copy the triangles of the leaves (same order as above)
-    const uint32_t qbase = n_int ? atomicAdd(&a.counters[2], n_int) : 0u;
+    const uint32_t qbase = n_int ? atomicAdd(qlen_out, n_int) : 0u;
     uint32_t r = 0, off = 0;
     for (int sl = 0; sl < 8; sl++) {
         const uint32_t k = (child_in >> (4 * sl)) & 0xfu;
@@ -584,6 +643,32 @@ __global__ void __launch_bounds__(COLLAPSE_THREADS) k_collapse(CollapseArgs a, c
             }
             off += cnt;
         }
+    }
+}
+
+// All levels in ONE cooperative kernel: level L reads queue L & 1 (length qlen[L % 3]), appends the internal children to the other
+// queue (length qlen[(L + 1) % 3]) and clears qlen[(L + 2) % 3] for the level after; a grid-wide barrier separates the levels.
+// Round 1 launched one kernel per level and read the next level's length back to the host (a stream synchronisation per level).
+// counters: [0] nodes allocated, [1] triangles allocated, [2..4] queue lengths.
+#define COLLAPSE_MAX_LEVELS 256
+__global__ void __launch_bounds__(COLLAPSE_THREADS) k_collapse_coop(CollapseArgs a, uint2* q0, uint2* q1, BuildStatus* st) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ CollapseShared sh;
+    uint32_t* qlen = a.counters + 2;
+    const uint32_t gtid = blockIdx.x * COLLAPSE_THREADS + threadIdx.x, gsize = gridDim.x * COLLAPSE_THREADS;
+    if (st->error) return;                               // uniform: written before this kernel started
+    uint32_t level = 0;
+    for (;; level++) {
+        const uint32_t n_in = *(volatile uint32_t*)&qlen[level % 3];
+        if (n_in == 0u || level >= COLLAPSE_MAX_LEVELS) break;
+        if (gtid == 0) qlen[(level + 2) % 3] = 0u;
+        const uint2* qin = (level & 1u) ? q1 : q0; uint2* qout = (level & 1u) ? q0 : q1;
+        for (uint32_t i = gtid; i < n_in; i += gsize) collapse_one(a, qin[i], qout, &qlen[(level + 1) % 3], sh);
+        grid.sync();
+    }
+    if (gtid == 0) {
+        st->n_nodes = a.counters[0]; st->n_tris = a.counters[1]; st->depth = level;
+        if (level >= COLLAPSE_MAX_LEVELS) atomicOr(&st->error, HJ_BUILD_ERR_COLLAPSE);
     }
 }
 
@@ -637,131 +722,212 @@ __global__ void k_verify_seen(const uint32_t* seen, uint32_t n, uint32_t* err) {
 // ---------------------------------------------------------------------------------------------- host driver
 static inline uint32_t cdiv(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
 
-int hj_bvh_build(hj_ctx* c, int mode) {
-    const uint32_t n = c->S.n_tris;
+__global__ void k_build_begin(BuildStatus* st, int* bounds) {
+    if (threadIdx.x == 0) { st->n_nodes = st->n_tris = st->depth = st->error = 0u; st->cur_n = st->node_ctr = st->pp = st->ploc_rounds = 0u; }
+    if (threadIdx.x < 3) bounds[threadIdx.x] = 0x7fffffff;
+    else if (threadIdx.x < 6) bounds[threadIdx.x] = (int)0x80000000;
+}
+__global__ void k_collapse_begin(uint32_t* counters, uint2* q0, uint32_t root) {
+    counters[0] = 1u; counters[1] = 0u; counters[2] = 1u; counters[3] = 0u; counters[4] = 0u;
+    q0[0] = make_uint2(root, 0u);
+}
+
+static int coop_grid(hj_ctx* c, const void* kernel, int threads, int& cache) {
+    if (cache > 0) return cache;
+    int occ = 0, sms = 148;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, threads, 0);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    cache = std::max(1, occ) * sms;
+    return cache;
+}
+
+// General 3x4 affine inverse by cofactors in float (the reference uses glm::inverse on the 4x4, renderer.h:272-284)
+static void invert_affine(const float* m, float* r) {
+    const float a = m[0], b = m[1], cc = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+    const float A = e * i - f * h, B = -(d * i - f * g), C = d * h - e * g;
+    const float det = a * A + b * B + cc * C;
+    const float id = 1.0f / det;
+    r[0] = A * id; r[1] = -(b * i - cc * h) * id; r[2] = (b * f - cc * e) * id;
+    r[4] = B * id; r[5] = (a * i - cc * g) * id; r[6] = -(a * f - cc * d) * id;
+    r[8] = C * id; r[9] = -(a * h - b * g) * id; r[10] = (a * e - b * d) * id;
+    const float tx = m[3], ty = m[7], tz = m[11];
+    r[3] = -(r[0] * tx + r[1] * ty + r[2] * tz);
+    r[7] = -(r[4] * tx + r[5] * ty + r[6] * tz);
+    r[11] = -(r[8] * tx + r[9] * ty + r[10] * tz);
+}
+
+// Enqueues ≙ updateIASMatrix (+ buildGAS/buildIAS in mode BUILD) for the set the renderer is NOT reading, on the build stream:
+// matrices H2D, flatten, [Morton, sort, PLOC | Karras + fit] or [refit: fit], collapse, status D2H. Not one host synchronisation:
+// loop control (PLOC rounds, collapse levels) lives in two cooperative kernels, results come back through a pinned status word.
+int hj_bvh_enqueue(hj_ctx* c, const float* xf, const float* inv_xf, int mode) {
+    const uint32_t n = c->S.n_tris, n_inst = c->S.n_instances;
     if (n == 0) { c->err = "hj_accel_build: scene has no triangles"; return HJ_ERR_INVALID; }
     BvhState& B = c->bvh;
-    cudaStream_t st = c->stream;
-    HJ_CUDA(c, c->d_tri_pos.reserve(3 * (size_t)n * sizeof(float4)));
-    HJ_CUDA(c, c->d_tri_attr.reserve(4 * (size_t)n * sizeof(float4)));
-    HJ_CUDA(c, B.bounds.reserve(8 * sizeof(int)));
-    c->S.tri_pos = c->d_tri_pos.as<float4>(); c->S.tri_attr = c->d_tri_attr.as<float4>();
-    HJ_CUDA(c, cudaEventRecord(c->ev0, st));
-    k_init_bounds<<<1, 32, 0, st>>>(B.bounds.as<int>());
-    k_flatten<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.bounds.as<int>());
+    if (!B.build_stream) {
+        int lo = 0, hi = 0; cudaDeviceGetStreamPriorityRange(&lo, &hi);          // lowest priority: a build yields to a frame in flight
+        HJ_CUDA(c, cudaStreamCreateWithPriority(&B.build_stream, cudaStreamNonBlocking, lo));
+        HJ_CUDA(c, cudaEventCreate(&B.ev_b0)); HJ_CUDA(c, cudaEventCreate(&B.ev_b1));
+        HJ_CUDA(c, cudaHostAlloc((void**)&B.h_status, sizeof(BuildStatus), cudaHostAllocDefault));
+    }
+    const int set = c->have_accel ? (c->accel_cur ^ 1) : c->accel_cur;
+    AccelSet& A = c->accel[set];
+    cudaStream_t st = B.build_stream;
+    // pinned staging of the matrices (the caller's arrays are borrowed for the call only)
+    if (B.h_xf_cap < 24 * (size_t)n_inst) {
+        if (B.h_xf) cudaFreeHost(B.h_xf);
+        B.h_xf = nullptr; B.h_xf_cap = 0;
+        HJ_CUDA(c, cudaHostAlloc((void**)&B.h_xf, 24 * (size_t)n_inst * sizeof(float), cudaHostAllocDefault));
+        B.h_xf_cap = 24 * (size_t)n_inst;
+    }
+    float* m = B.h_xf; float* im = B.h_xf + 12 * (size_t)n_inst;
+    for (uint32_t i = 0; i < n_inst; i++) {
+        float* p = m + 12 * (size_t)i; float* q = im + 12 * (size_t)i;
+        if (xf) memcpy(p, xf + 12 * (size_t)i, 48);
+        else { memset(p, 0, 48); p[0] = p[5] = p[10] = 1.0f; }
+        if (inv_xf) memcpy(q, inv_xf + 12 * (size_t)i, 48);
+        else if (xf) invert_affine(p, q);
+        else memcpy(q, p, 48);
+    }
+    HJ_CUDA(c, A.xf.reserve(48 * (size_t)n_inst)); HJ_CUDA(c, A.inv_xf.reserve(48 * (size_t)n_inst));
+    HJ_CUDA(c, A.tri_pos.reserve(3 * (size_t)n * sizeof(float4))); HJ_CUDA(c, A.tri_attr.reserve(4 * (size_t)n * sizeof(float4)));
+    HJ_CUDA(c, A.nodes.reserve((size_t)n * 16 * HJ_NODE_QUADS)); HJ_CUDA(c, A.btris.reserve(3 * (size_t)n * sizeof(float4)));
+    HJ_CUDA(c, B.bounds.reserve(8 * sizeof(int))); HJ_CUDA(c, B.status.reserve(sizeof(BuildStatus)));
+    if (!A.ev_last_read) HJ_CUDA(c, cudaEventCreateWithFlags(&A.ev_last_read, cudaEventDisableTiming));
+    else HJ_CUDA(c, cudaStreamWaitEvent(st, A.ev_last_read, 0));                 // frames that still read this set finish first
+    HJ_CUDA(c, cudaStreamWaitEvent(st, c->ev_scene, 0));                         // the scene upload on the context stream
+    DevScene S = c->S;                                                           // the scene as the build kernels see it: target set
+    S.xf = A.xf.as<float4>(); S.inv_xf = A.inv_xf.as<float4>(); S.tri_pos = A.tri_pos.as<float4>(); S.tri_attr = A.tri_attr.as<float4>();
+    BuildStatus* dst = B.status.as<BuildStatus>();
+    HJ_CUDA(c, cudaEventRecord(B.ev_b0, st));
+    HJ_CUDA(c, cudaMemcpyAsync(A.xf.p, m, 48 * (size_t)n_inst, cudaMemcpyHostToDevice, st));
+    HJ_CUDA(c, cudaMemcpyAsync(A.inv_xf.p, im, 48 * (size_t)n_inst, cudaMemcpyHostToDevice, st));
+    k_build_begin<<<1, 32, 0, st>>>(dst, B.bounds.as<int>());
+    k_flatten<<<cdiv(n, 256), 256, 0, st>>>(S, B.bounds.as<int>(), &dst->error);
     const bool topo = (mode == HJ_ACCEL_BUILD) || !B.have_topology;
+    uint32_t root = 0;
     if (topo) {
         const uint32_t nb = cdiv(n, RS_TILE);
         HJ_CUDA(c, B.keys.reserve((size_t)n * 8)); HJ_CUDA(c, B.keys_alt.reserve((size_t)n * 8));
         HJ_CUDA(c, B.vals.reserve((size_t)n * 4)); HJ_CUDA(c, B.vals_alt.reserve((size_t)n * 4));
-        HJ_CUDA(c, B.block_hist.reserve((size_t)256 * nb * 4));
+        HJ_CUDA(c, B.block_hist.reserve((size_t)256 * nb * 4)); HJ_CUDA(c, B.digit_total.reserve(256 * 4));
         HJ_CUDA(c, B.left.reserve((size_t)n * 4)); HJ_CUDA(c, B.right.reserve((size_t)n * 4));
         HJ_CUDA(c, B.parent.reserve(2 * (size_t)n * 4));
-        k_morton<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.bounds.as<int>(), B.keys.as<uint64_t>(), B.vals.as<uint32_t>());
+        k_morton<<<cdiv(n, 256), 256, 0, st>>>(S, B.bounds.as<int>(), B.keys.as<uint64_t>(), B.vals.as<uint32_t>());
         uint64_t *k0 = B.keys.as<uint64_t>(), *k1 = B.keys_alt.as<uint64_t>();
         uint32_t *v0 = B.vals.as<uint32_t>(), *v1 = B.vals_alt.as<uint32_t>();
         for (int pass = 0; pass < 8; pass++) {      // 63-bit keys: 8 passes of 8 bits, result back in k0/v0
             k_rs_hist<<<nb, RS_THREADS, 0, st>>>(k0, n, 8 * pass, B.block_hist.as<uint32_t>(), nb);
-            k_rs_scan<<<1, 1024, 0, st>>>(B.block_hist.as<uint32_t>(), 256 * nb);
-            k_rs_scatter<<<nb, RS_THREADS, 0, st>>>(k0, v0, n, 8 * pass, B.block_hist.as<uint32_t>(), nb, k1, v1);
+            k_rs_scan_rows<<<256, RS_SCAN_THREADS, 0, st>>>(B.block_hist.as<uint32_t>(), nb, B.digit_total.as<uint32_t>());
+            k_rs_scatter<<<nb, RS_THREADS, 0, st>>>(k0, v0, n, 8 * pass, B.block_hist.as<uint32_t>(), B.digit_total.as<uint32_t>(), nb, k1, v1);
             std::swap(k0, k1); std::swap(v0, v1);
         }
         HJ_CUDA(c, B.cnt.reserve((size_t)n * 4));
         HJ_CUDA(c, B.blo.reserve(2 * (size_t)n * sizeof(float4))); HJ_CUDA(c, B.bhi.reserve(2 * (size_t)n * sizeof(float4)));
-        B.root = 0;
         if (n > 1 && c->opt_builder == 0) {
             k_karras<<<cdiv(n - 1, 256), 256, 0, st>>>(B.keys.as<uint64_t>(), (int)n, B.left.as<uint32_t>(), B.right.as<uint32_t>(),
                                                        B.parent.as<uint32_t>(), B.cnt.as<uint32_t>());
         } else if (n > 1) {
-            const uint32_t nbmax = cdiv(n, PLOC_THREADS);
+            const int grid = std::min<int>(coop_grid(c, (const void*)k_ploc_coop, PLOC_THREADS, B.coop_blocks_ploc), (int)cdiv(n, PLOC_THREADS));
             HJ_CUDA(c, B.p_cid[0].reserve((size_t)n * 4)); HJ_CUDA(c, B.p_cid[1].reserve((size_t)n * 4));
             for (int k = 0; k < 2; k++) { HJ_CUDA(c, B.p_lo[k].reserve((size_t)n * 16)); HJ_CUDA(c, B.p_hi[k].reserve((size_t)n * 16)); }
-            HJ_CUDA(c, B.p_nn.reserve((size_t)n * 4)); HJ_CUDA(c, B.p_keep.reserve((size_t)n * 4));
-            HJ_CUDA(c, B.p_bcount.reserve(((size_t)nbmax + 1) * 4)); HJ_CUDA(c, B.counters.reserve(4 * sizeof(uint32_t)));
-            HJ_CUDA(c, cudaMemsetAsync(B.counters.p, 0, 16, st));
-            k_ploc_init<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.vals.as<uint32_t>(), (int)n, B.p_cid[0].as<uint32_t>(), B.p_lo[0].as<float4>(), B.p_hi[0].as<float4>(),
+            HJ_CUDA(c, B.p_nn.reserve((size_t)n * 4));
+            HJ_CUDA(c, B.p_keep.reserve((size_t)B.coop_blocks_ploc * 4)); HJ_CUDA(c, B.p_bcount.reserve((size_t)B.coop_blocks_ploc * 4));
+            k_ploc_init<<<cdiv(n, 256), 256, 0, st>>>(S, B.vals.as<uint32_t>(), (int)n, B.p_cid[0].as<uint32_t>(), B.p_lo[0].as<float4>(), B.p_hi[0].as<float4>(),
                                                       B.blo.as<float4>(), B.bhi.as<float4>());
-            uint32_t cur_n = n; int pp = 0, rounds = 0;
-            while (cur_n > 1) {
-                if (cur_n <= PLOC_TAIL && c->opt_ploc_tail) {            // the remaining rounds in one block, no host round trips
-                    k_ploc_tail<<<1, PLOC_TAIL, 0, st>>>((int)cur_n, (int)n, B.p_cid[pp].as<uint32_t>(), B.p_lo[pp].as<float4>(), B.p_hi[pp].as<float4>(), B.counters.as<uint32_t>(),
-                                                         B.left.as<uint32_t>(), B.right.as<uint32_t>(), B.parent.as<uint32_t>(), B.cnt.as<uint32_t>(), B.blo.as<float4>(), B.bhi.as<float4>());
-                    break;
-                }
-                const uint32_t nb = cdiv(cur_n, PLOC_THREADS);
-                k_ploc_nn<<<nb, PLOC_THREADS, 0, st>>>((int)cur_n, B.p_lo[pp].as<float4>(), B.p_hi[pp].as<float4>(), B.p_nn.as<uint32_t>());
-                k_ploc_merge<<<nb, PLOC_THREADS, 0, st>>>((int)cur_n, (int)n, B.p_cid[pp].as<uint32_t>(), B.p_lo[pp].as<float4>(), B.p_hi[pp].as<float4>(), B.p_nn.as<uint32_t>(),
-                                                          B.counters.as<uint32_t>(), B.left.as<uint32_t>(), B.right.as<uint32_t>(), B.parent.as<uint32_t>(), B.cnt.as<uint32_t>(),
-                                                          B.blo.as<float4>(), B.bhi.as<float4>(), B.p_keep.as<uint32_t>(), B.p_bcount.as<uint32_t>());
-                HJ_CUDA(c, cudaMemsetAsync(B.p_bcount.as<uint32_t>() + nb, 0, 4, st));
-                k_rs_scan<<<1, 1024, 0, st>>>(B.p_bcount.as<uint32_t>(), nb + 1);
-                k_ploc_compact<<<nb, PLOC_THREADS, 0, st>>>((int)cur_n, B.p_keep.as<uint32_t>(), B.p_bcount.as<uint32_t>(), B.p_cid[pp].as<uint32_t>(), B.p_lo[pp].as<float4>(),
-                                                            B.p_hi[pp].as<float4>(), B.p_cid[pp ^ 1].as<uint32_t>(), B.p_lo[pp ^ 1].as<float4>(), B.p_hi[pp ^ 1].as<float4>());
-                uint32_t next_n = 0;
-                HJ_CUDA(c, cudaMemcpyAsync(&next_n, B.p_bcount.as<uint32_t>() + nb, 4, cudaMemcpyDeviceToHost, st));
-                HJ_CUDA(c, cudaStreamSynchronize(st));
-                if (next_n >= cur_n || next_n == 0 || ++rounds > 4096) { c->err = "hj_accel_build: PLOC made no progress"; return HJ_ERR_INVALID; }
-                cur_n = next_n; pp ^= 1;
-            }
-            B.root = n - 2;      // the last merge allocated the last internal id
-            const uint32_t none = 0xffffffffu;
-            HJ_CUDA(c, cudaMemcpyAsync(B.parent.as<uint32_t>() + B.root, &none, 4, cudaMemcpyHostToDevice, st));
-            B.ploc_rounds = rounds;
+            PlocArgs P;
+            P.n = (int)n; P.tail_at = c->opt_ploc_tail ? PLOC_TAIL : 1;
+            for (int k = 0; k < 2; k++) { P.cid[k] = B.p_cid[k].as<uint32_t>(); P.clo[k] = B.p_lo[k].as<float4>(); P.chi[k] = B.p_hi[k].as<float4>(); }
+            P.nn = B.p_nn.as<int>(); P.bkeep = B.p_keep.as<uint32_t>(); P.bmerge = B.p_bcount.as<uint32_t>();
+            P.left = B.left.as<uint32_t>(); P.right = B.right.as<uint32_t>(); P.parent = B.parent.as<uint32_t>(); P.cnt = B.cnt.as<uint32_t>();
+            P.blo = B.blo.as<float4>(); P.bhi = B.bhi.as<float4>(); P.st = dst;
+            void* args[] = {&P};
+            HJ_CUDA(c, cudaLaunchCooperativeKernel((const void*)k_ploc_coop, dim3((unsigned)grid), dim3(PLOC_THREADS), args, 0, st));
+            k_ploc_tail<<<1, PLOC_TAIL, 0, st>>>(P);
+            root = n - 2;        // ids are handed out in order: the last merge made the root
         }
-        B.have_topology = true;
+    } else root = (n > 1 && c->opt_builder == 1) ? n - 2 : 0;
+    if (!topo || c->opt_builder == 0 || n == 1) {   // PLOC computes the boxes while it merges; a refit recomputes them bottom-up
+        HJ_CUDA(c, B.flags.reserve((size_t)n * 4));
+        HJ_CUDA(c, cudaMemsetAsync(B.flags.p, 0, (size_t)n * 4, st));
+        k_fit<<<cdiv(n, 256), 256, 0, st>>>(S, B.vals.as<uint32_t>(), (int)n, B.left.as<uint32_t>(), B.right.as<uint32_t>(), B.parent.as<uint32_t>(),
+                                            B.flags.as<uint32_t>(), B.blo.as<float4>(), B.bhi.as<float4>());
     }
-    HJ_CUDA(c, B.flags.reserve((size_t)n * 4));
-    HJ_CUDA(c, cudaMemsetAsync(B.flags.p, 0, (size_t)n * 4, st));
-    if (!topo || c->opt_builder == 0 || n == 1)     // PLOC computes the boxes while it merges; a refit recomputes them bottom-up
-    k_fit<<<cdiv(n, 256), 256, 0, st>>>(c->S, B.vals.as<uint32_t>(), (int)n, B.left.as<uint32_t>(), B.right.as<uint32_t>(), B.parent.as<uint32_t>(),
-                                        B.flags.as<uint32_t>(), B.blo.as<float4>(), B.bhi.as<float4>());
-    // collapse, level by level
-    HJ_CUDA(c, B.nodes.reserve((size_t)n * 16 * HJ_NODE_QUADS)); HJ_CUDA(c, B.btris.reserve(3 * (size_t)n * sizeof(float4)));
+    // collapse: all levels in one cooperative kernel
     HJ_CUDA(c, B.queue_a.reserve((size_t)n * sizeof(uint2))); HJ_CUDA(c, B.queue_b.reserve((size_t)n * sizeof(uint2)));
-    HJ_CUDA(c, B.counters.reserve(4 * sizeof(uint32_t)));
-    const uint32_t init_counters[4] = {1u, 0u, 0u, 0u};
-    const uint2 root = make_uint2(B.root, 0u);
-    HJ_CUDA(c, cudaMemcpyAsync(B.counters.p, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, st));
-    HJ_CUDA(c, cudaMemcpyAsync(B.queue_a.p, &root, sizeof root, cudaMemcpyHostToDevice, st));
+    HJ_CUDA(c, B.counters.reserve(8 * sizeof(uint32_t)));
+    k_collapse_begin<<<1, 1, 0, st>>>(B.counters.as<uint32_t>(), B.queue_a.as<uint2>(), root);
     CollapseArgs a;
     a.n = (int)n; a.leaf_max = (uint32_t)c->opt_leaf_max; a.leaf_split = c->opt_leaf_split;
     a.left = B.left.as<uint32_t>(); a.right = B.right.as<uint32_t>(); a.cnt = B.cnt.as<uint32_t>();
-    a.sorted = B.vals.as<uint32_t>(); a.blo = B.blo.as<float4>(); a.bhi = B.bhi.as<float4>(); a.tri_pos = c->S.tri_pos;
-    a.nodes = B.nodes.as<uint4>(); a.btris = B.btris.as<float4>(); a.counters = B.counters.as<uint32_t>();
-    uint2 *qi = B.queue_a.as<uint2>(), *qo = B.queue_b.as<uint2>();
-    uint32_t n_in = 1, depth = 0, cnt[4];
-    while (n_in) {
-        HJ_CUDA(c, cudaMemsetAsync(a.counters + 2, 0, 4, st));
-        k_collapse<<<cdiv(n_in, COLLAPSE_THREADS), COLLAPSE_THREADS, 0, st>>>(a, qi, n_in, qo);
-        HJ_CUDA(c, cudaMemcpyAsync(cnt, a.counters, sizeof cnt, cudaMemcpyDeviceToHost, st));
-        HJ_CUDA(c, cudaStreamSynchronize(st));
-        n_in = cnt[2]; std::swap(qi, qo); depth++;
-        if (depth > 4096) { c->err = "hj_accel_build: collapse did not terminate"; return HJ_ERR_INVALID; }
+    a.sorted = B.vals.as<uint32_t>(); a.blo = B.blo.as<float4>(); a.bhi = B.bhi.as<float4>(); a.tri_pos = S.tri_pos;
+    a.nodes = A.nodes.as<uint4>(); a.btris = A.btris.as<float4>(); a.counters = B.counters.as<uint32_t>();
+    {
+        const int grid = std::min<int>(coop_grid(c, (const void*)k_collapse_coop, COLLAPSE_THREADS, B.coop_blocks_collapse), (int)cdiv(n, COLLAPSE_THREADS));
+        uint2* q0 = B.queue_a.as<uint2>(); uint2* q1 = B.queue_b.as<uint2>();
+        void* args[] = {&a, &q0, &q1, &dst};
+        HJ_CUDA(c, cudaLaunchCooperativeKernel((const void*)k_collapse_coop, dim3((unsigned)grid), dim3(COLLAPSE_THREADS), args, 0, st));
     }
-    HJ_CUDA(c, cudaEventRecord(c->ev1, st));
-    HJ_CUDA(c, cudaEventSynchronize(c->ev1));
+    HJ_CUDA(c, cudaMemcpyAsync(B.h_status, dst, sizeof(BuildStatus), cudaMemcpyDeviceToHost, st));
+    HJ_CUDA(c, cudaEventRecord(B.ev_b1, st));
     HJ_CUDA(c, cudaGetLastError());
-    float ms = 0; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    B.pending_set = set; B.pending_mode = mode; B.pending_topo = topo;
+    return HJ_OK;
+}
+
+// Waits for the build in flight (if any), validates what the device reported and makes its buffers the ones frames read.
+int hj_bvh_finish(hj_ctx* c) {
+    BvhState& B = c->bvh;
+    if (B.pending_set < 0) return HJ_OK;
+    const int set = B.pending_set; B.pending_set = -1;
+    AccelSet& A = c->accel[set];
+    const uint32_t n = c->S.n_tris;
+    HJ_CUDA(c, cudaEventSynchronize(B.ev_b1));
+    HJ_CUDA(c, cudaGetLastError());
+    const BuildStatus h = *B.h_status;
+    float ms = 0; cudaEventElapsedTime(&ms, B.ev_b0, B.ev_b1);
+    auto fail = [&](const std::string& msg) { if (B.pending_topo) B.have_topology = false; c->err = msg; return HJ_ERR_INVALID; };
+    if (h.error & HJ_BUILD_ERR_NONFINITE) return fail("hj_accel_build: a vertex is not finite after the instance transform (NaN / inf in the vertices or matrices)");
+    if (h.error & HJ_BUILD_ERR_PLOC) return fail("hj_accel_build: PLOC made no progress (non-finite bounding boxes)");
+    if (h.error & HJ_BUILD_ERR_COLLAPSE) return fail("hj_accel_build: collapse did not terminate");
+    if (h.n_tris != n) return fail("hj_accel_build: internal error, leaf triangles != scene triangles");
+    if (2 * h.depth > HJ_STACK) {
+        char b[160]; snprintf(b, sizeof b, "hj_accel_build: wide BVH depth %u exceeds the traversal stack (%d)", h.depth, HJ_STACK);
+        return fail(b);
+    }
+    if (B.pending_topo) { B.have_topology = true; B.ploc_rounds = (int)h.ploc_rounds; }
     if (c->opt_verify_accel) {      // structural check of the wide BVH (k_verify); the tests switch it on
-        uint32_t h[2] = {0, 0};
-        HJ_CUDA(c, B.verr.reserve(8));
+        cudaStream_t st = B.build_stream;
+        uint32_t e[2] = {0, 0};
+        HJ_CUDA(c, B.verr.reserve(8)); HJ_CUDA(c, B.flags.reserve((size_t)n * 4));
         HJ_CUDA(c, cudaMemsetAsync(B.flags.p, 0, (size_t)n * 4, st)); HJ_CUDA(c, cudaMemsetAsync(B.verr.p, 0, 8, st));
-        k_verify<<<cdiv(cnt[0], 128), 128, 0, st>>>(B.nodes.as<uint4>(), B.btris.as<float4>(), cnt[0], n, B.flags.as<uint32_t>(), B.verr.as<uint32_t>());
+        k_verify<<<cdiv(h.n_nodes, 128), 128, 0, st>>>(A.nodes.as<uint4>(), A.btris.as<float4>(), h.n_nodes, n, B.flags.as<uint32_t>(), B.verr.as<uint32_t>());
         k_verify_seen<<<cdiv(n, 256), 256, 0, st>>>(B.flags.as<uint32_t>(), n, B.verr.as<uint32_t>());
-        HJ_CUDA(c, cudaMemcpyAsync(h, B.verr.p, 8, cudaMemcpyDeviceToHost, st));
+        HJ_CUDA(c, cudaMemcpyAsync(e, B.verr.p, 8, cudaMemcpyDeviceToHost, st));
         HJ_CUDA(c, cudaStreamSynchronize(st));
-        if (h[0]) {
-            char b[200]; snprintf(b, sizeof b, "hj_accel_build: verify_accel found an inconsistent BVH (error bits 0x%x, %u primitives not in exactly one leaf)", h[0], h[1]);
-            c->err = b; return HJ_ERR_INVALID;
+        if (e[0]) {
+            char b[200]; snprintf(b, sizeof b, "hj_accel_build: verify_accel found an inconsistent BVH (error bits 0x%x, %u primitives not in exactly one leaf)", e[0], e[1]);
+            return fail(b);
         }
     }
-    if (cnt[1] != n) { c->err = "hj_accel_build: internal error, leaf triangles != scene triangles"; return HJ_ERR_INVALID; }
-    if (2 * depth > HJ_STACK) {
-        char b[160]; snprintf(b, sizeof b, "hj_accel_build: wide BVH depth %u exceeds the traversal stack (%d)", depth, HJ_STACK);
-        c->err = b; return HJ_ERR_INVALID;
-    }
-    B.n_nodes = cnt[0]; B.depth = depth;
-    c->S.nodes = B.nodes.as<uint4>(); c->S.btris = B.btris.as<float4>();
-    c->stats.ms_accel = ms; c->stats.bvh_nodes = B.n_nodes; c->stats.bvh_node_bytes = 16 * HJ_NODE_QUADS; c->stats.bvh_depth = depth;
+    A.n_nodes = h.n_nodes; A.depth = h.depth;
+    c->accel_cur = set;
+    c->S.xf = A.xf.as<float4>(); c->S.inv_xf = A.inv_xf.as<float4>(); c->S.tri_pos = A.tri_pos.as<float4>(); c->S.tri_attr = A.tri_attr.as<float4>();
+    c->S.nodes = A.nodes.as<uint4>(); c->S.btris = A.btris.as<float4>();
+    c->have_accel = true;
+    c->stats.ms_accel = ms; c->stats.bvh_nodes = A.n_nodes; c->stats.bvh_node_bytes = 16 * HJ_NODE_QUADS; c->stats.bvh_depth = A.depth;
     return HJ_OK;
+}
+
+void hj_bvh_release(hj_ctx* c) {
+    BvhState& B = c->bvh;
+    if (B.build_stream) { cudaStreamSynchronize(B.build_stream); cudaStreamDestroy(B.build_stream); B.build_stream = nullptr; }
+    if (B.ev_b0) cudaEventDestroy(B.ev_b0);
+    if (B.ev_b1) cudaEventDestroy(B.ev_b1);
+    if (B.h_status) cudaFreeHost(B.h_status);
+    if (B.h_xf) cudaFreeHost(B.h_xf);
+    for (AccelSet& A : c->accel) {
+        DevBuf* bufs[] = {&A.xf, &A.inv_xf, &A.tri_pos, &A.tri_attr, &A.nodes, &A.btris};
+        for (DevBuf* b : bufs) b->release();
+        if (A.ev_last_read) cudaEventDestroy(A.ev_last_read);
+    }
 }

@@ -24,9 +24,21 @@ struct DevBuf {
     template <class T> T* as() const { return (T*)p; }
 };
 
+// Everything a frame reads of the acceleration structure. Two sets: hj_accel_build_async fills the one the renderer is not
+// reading (on its own stream, under the previous frame's shading) and the next hj_render flips to it (the
+// reference updates its IAS inside the frame loop, renderer.h:257-291,1126-1133).
+struct AccelSet {
+    DevBuf xf, inv_xf;            // 3 float4 rows per instance and the rows of the inverse
+    DevBuf tri_pos, tri_attr;     // world-space flattening (k_flatten)
+    DevBuf nodes, btris;          // the traversal structure
+    uint32_t n_nodes = 0, depth = 0;
+    cudaEvent_t ev_last_read = nullptr;   // end of the last frame that read this set: a build into it waits for that
+};
+struct BuildStatus;
+
 struct BvhState {
     // binary LBVH (Karras 2012), N leaves = triangles in Morton order
-    DevBuf keys, keys_alt, vals, vals_alt, block_hist;
+    DevBuf keys, keys_alt, vals, vals_alt, block_hist, digit_total;
     DevBuf blo, bhi;              // float4[2N-1] boxes: internal i -> i, leaf j -> N-1+j
     DevBuf left, right, parent;   // uint32
     DevBuf cnt, flags;            // uint32[N-1]: leaves below an internal node; fit counters
@@ -34,9 +46,14 @@ struct BvhState {
     uint32_t root = 0; int ploc_rounds = 0;
     DevBuf bounds;                // 6 ordered-int atomics
     DevBuf queue_a, queue_b, counters, verr;   // collapse work queues: uint2 {binary node, wide node}
-    DevBuf nodes, btris;          // the traversal structure
-    uint32_t n_nodes = 0, depth = 0;
+    DevBuf status;                // BuildStatus written by the build kernels; h_status = its pinned host mirror
+    BuildStatus* h_status = nullptr;
+    float* h_xf = nullptr; size_t h_xf_cap = 0;   // pinned staging of the instance matrices (2 x 12 floats per instance)
     bool have_topology = false;
+    // the build in flight (enqueued on build_stream, not yet validated / flipped to)
+    int pending_set = -1; int pending_mode = 0; bool pending_topo = false;
+    cudaStream_t build_stream = nullptr; cudaEvent_t ev_b0 = nullptr, ev_b1 = nullptr;
+    int coop_blocks_ploc = 0, coop_blocks_collapse = 0;
 };
 
 #define HJ_MAX_PIPES 8
@@ -61,7 +78,7 @@ struct NcclApi;
 struct hj_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_scene = nullptr;   // ev_scene: end of the last hj_scene_upload on `stream`
     std::string err;
     // options
     int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3, opt_trace_blocks_per_sm = 0, opt_pipelines = 8, opt_builder = 1, opt_mis_emitter_first = 1, opt_leaf_split = 1, opt_verify_accel = 0, opt_bands = 0, opt_ploc_tail = 1;   // builder: 0 Karras radix tree (LBVH), 1 PLOC
@@ -70,8 +87,8 @@ struct hj_ctx {
     bool have_scene = false, have_accel = false, have_frame = false;
     DevScene S{};                 // device pointers (host copy of the struct, passed to kernels by value)
     DevBuf d_vertices, d_normals, d_texcoords, d_indices, d_material_ids, d_prim_offsets, d_tri_inst;
-    DevBuf d_xf, d_inv_xf, d_materials, d_textures, d_texels, d_srgb, d_light_ids, d_light_em, d_ibl, d_lut;
-    DevBuf d_tri_pos, d_tri_attr;
+    DevBuf d_materials, d_textures, d_texels, d_srgb, d_light_ids, d_light_em, d_ibl, d_lut;
+    AccelSet accel[2]; int accel_cur = 0;      // S points into accel[accel_cur]
     BvhState bvh;
     WavefrontState wf[HJ_MAX_PIPES];
     int n_pipes_used = 0;
@@ -104,8 +121,10 @@ struct hj_ctx {
         }                                                                                          \
     } while (0)
 
-// hj_bvh.cu
-int hj_bvh_build(hj_ctx* c, int mode);
+// hj_bvh.cu: enqueue a build of accel[set] on the build stream (no host synchronisation); finish = wait, validate, flip
+int hj_bvh_enqueue(hj_ctx* c, const float* xf3x4, const float* inv3x4, int mode);
+int hj_bvh_finish(hj_ctx* c);
+void hj_bvh_release(hj_ctx* c);
 // hj_wavefront.cu
 int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp);
 int hj_wavefront_finalize(hj_ctx* c);

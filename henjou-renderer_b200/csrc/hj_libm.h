@@ -203,6 +203,17 @@ HJM_FN float hjm_powf(float x, float y) {
         return (neg && y_odd) ? -mag : mag;
     }
     if (neg && !y_int) return hjm_nanf();
+    if (y_int && ay <= 8.0f) {
+        // small integer exponents (the Schlick terms pow(1 - cos, 5) of math.h:26-37 are most of the calls): repeated multiplication
+        // in double — three or four roundings at 1e-16, then one rounding to float; no log / exp, the sign comes out by itself
+        const double xd = (double)x, x2 = xd * xd, x4 = x2 * x2;
+        const uint32_t k = (uint32_t)ay;
+        double p = (k & 1u) ? xd : 1.0;
+        if (k & 2u) p *= x2;
+        if (k & 4u) p *= x4;
+        if (k & 8u) p *= x4 * x4;
+        return (float)(y > 0.0f ? p : 1.0 / p);
+    }
     const float r = (float)hjm_exp_d((double)y * hjm_log_pos((double)ax));
     return (neg && y_odd) ? -r : r;
 }

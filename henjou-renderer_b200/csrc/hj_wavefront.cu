@@ -5,10 +5,11 @@
 //
 // One path per slot; slot = s_local * W*H + pixel, so the RNG stream of a path is CMJState{n_spp = global sample
 // index, scramble = frame, image_idx = pixel} regardless of how samples are sliced over passes or GPUs.
-// Per bounce:   k_extend (closest hit)  ->  k_shade (surface, NEE sample, MIS sample, continuation, Russian
-// roulette; pushes shadow / MIS / next-bounce queues with warp-aggregated atomics)  ->  k_shadow (any hit)  ->
-// k_mis (closest hit + emitter evaluation). Queue lengths live in device memory and every kernel is a
-// grid-stride loop over its queue, so a frame is enqueued without a single host synchronisation.
+// Per bounce:   k_trace<0> (closest hit)  ->  k_surface (closest-hit / miss programs, sort into BSDF-class queues)  ->  k_nee
+// (light sample + BSDF evaluation -> shadow queue)  ->  k_sample<class> (MIS sample -> MIS queue, continuation sample, Russian
+// roulette -> next-bounce queue; warp-aggregated pushes)  ->  k_trace<1> (any hit)  ->  k_trace<3> (MIS emitter ray). Queue
+// lengths live in device memory and every kernel is a grid-stride loop over its queue, so a frame is enqueued without a single
+// host synchronisation.
 // The draw order of every RNG dimension and the order of the float additions into the radiance follow the
 // reference loop exactly; rays whose contribution is exactly zero are not traced (they cannot change the result).
 #include "hj_ctx.h"
@@ -701,6 +702,7 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     k_finalize<<<cdiv_u(WH, 256), 256, 0, st>>>(F, c->aov_accum.as<float4>(), c->aov_color.as<float4>(), c->aov_rgba8.as<uchar4>());
     launches++;
     HJ_CUDA(c, cudaEventRecord(c->ev1, st));
+    if (c->accel[c->accel_cur].ev_last_read) HJ_CUDA(c, cudaEventRecord(c->accel[c->accel_cur].ev_last_read, st));   // a later build into this set waits for this frame
     HJ_CUDA(c, cudaGetLastError());
     c->fp = *fp; c->have_frame = true; c->have_output = false;
     c->stats.kernel_launches = launches;

@@ -201,18 +201,30 @@ int main(int argc, char** argv) {
     };
     int n_done = 0;
     bool first = true;
-    for (int frame = opt.start_frame; frame < opt.end_frame; frame++) {          // renderer.h:1126
+    // The acceleration structure of frame N+1 is updated on the library's build stream while frame N is shaded
+    // (hj_accel_build_async right after hj_render_async): the reference does updateIASMatrix at the top of each iteration
+    // (renderer.h:1133) and stalls on it.
+    auto enqueue_accel = [&](int frame, bool blocking) -> int {
         const float time = frame / float(opt.fps);                                // :1128
         std::vector<float> xf, inv;
         instance_matrices(sc, time, xf, inv);                                     // updateIASMatrix, :1133
-        HJ_CHECK(ctx, hj_accel_build(ctx, xf.data(), inv.data(), sc.n_instances(), (first || rebuild) ? HJ_ACCEL_BUILD : HJ_ACCEL_REFIT));
+        const int mode = (first || rebuild) ? HJ_ACCEL_BUILD : HJ_ACCEL_REFIT;
+        return blocking ? hj_accel_build(ctx, xf.data(), inv.data(), sc.n_instances(), mode)
+                        : hj_accel_build_async(ctx, xf.data(), inv.data(), sc.n_instances(), mode);
+    };
+    HJ_CHECK(ctx, enqueue_accel(opt.start_frame, true));
+    first = false;
+    for (int frame = opt.start_frame; frame < opt.end_frame; frame++) {          // renderer.h:1126
+        const float time = frame / float(opt.fps);                                // :1128
         hj_frame_params fp{};
         fp.width = in_w; fp.height = in_h;
         fp.spp = opt.max_spp; fp.sample_begin = 0; fp.sample_end = opt.max_spp; fp.frame = (uint32_t)frame;      // :1186-1187
         camera_basis(opt, sc, time, fp);
         fp.ibl_intensity = opt.IBL_intensity;
         fp.integrator = opt.integrator; fp.max_depth = opt.max_depth; fp.tonemap = opt.tonemap; fp.pixel_jitter = 1;
-        HJ_CHECK(ctx, hj_render(ctx, &fp));                                       // optixLaunch + sync, :1241-1242
+        HJ_CHECK(ctx, hj_render_async(ctx, &fp));                                 // optixLaunch, :1241
+        if (frame + 1 < opt.end_frame) HJ_CHECK(ctx, enqueue_accel(frame + 1, false));   // next frame's update under this frame's shading
+        HJ_CHECK(ctx, hj_sync(ctx));                                              // CUDA_SYNC_CHECK, :1242
         HJ_CHECK(ctx, hj_post(ctx, post_mode));                                   // denosier_manager.denoise(), :1262-1271
         std::vector<uint8_t>& rgba = rgba_buf[n_done & 1];                        // its previous user (frame N-2) was joined below
         HJ_CHECK(ctx, hj_readback(ctx, HJ_AOV_OUTPUT_RGBA8, rgba.data(), rgba.size()));   // float4ConvertColor(AOV_Output), :1281
@@ -228,7 +240,6 @@ int main(int argc, char** argv) {
         const double el = now_s() - t_start;
         LOGI("frame %d: accel %.2f ms, render %.2f ms, post %.2f ms, %.1f Mrays/s -> %s   (time limit: %.1f s / %.1f s)", frame, st.ms_accel, st.ms_render, st.ms_post,
              (st.rays_extend + st.rays_shadow) / (st.ms_render * 1e3), name.c_str(), el, opt.time_limit * 60.0f);
-        first = false;
         // the check the reference carries commented out (renderer.h:1247-1254): stop once the sequence is over its budget
         if (enforce_limit && el > opt.time_limit * 60.0f) { LOGI("Over Time Limit: %d of %d frames written", n_done, opt.end_frame - opt.start_frame); break; }
     }

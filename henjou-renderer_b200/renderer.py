@@ -37,6 +37,8 @@ def load_library():
     L.hj_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
     L.hj_scene_upload.argtypes = [vp, C.POINTER(abi.hj_scene_desc)]
     L.hj_accel_build.argtypes = [vp, abi.f32p, abi.f32p, C.c_uint32, C.c_int]
+    L.hj_accel_build_async.argtypes = [vp, abi.f32p, abi.f32p, C.c_uint32, C.c_int]
+    L.hj_accel_wait.argtypes = [vp]
     L.hj_render.argtypes = [vp, C.POINTER(abi.hj_frame_params)]
     L.hj_render_async.argtypes = [vp, C.POINTER(abi.hj_frame_params)]
     L.hj_sync.argtypes = [vp]
@@ -82,11 +84,19 @@ class Renderer:
         desc = scene.to_desc()
         self._check(self.L.hj_scene_upload(self.ctx, C.byref(desc)), "hj_scene_upload")
 
-    def build_accel(self, xforms=None, inv_xforms=None, mode=abi.ACCEL_BUILD):
+    def build_accel(self, xforms=None, inv_xforms=None, mode=abi.ACCEL_BUILD, sync=True):
+        """sync=False: hj_accel_build_async — enqueued on the build stream into the second buffer set (it may run under a frame
+        in flight); the next render / trace / accel_wait completes it."""
         xf = None if xforms is None else np.ascontiguousarray(xforms, np.float32)
         ixf = None if inv_xforms is None else np.ascontiguousarray(inv_xforms, np.float32)
         p = lambda a: a.ctypes.data_as(abi.f32p) if a is not None else None
-        self._check(self.L.hj_accel_build(self.ctx, p(xf), p(ixf), self.scene.n_instances, mode), "hj_accel_build")
+        if sync:
+            self._check(self.L.hj_accel_build(self.ctx, p(xf), p(ixf), self.scene.n_instances, mode), "hj_accel_build")
+        else:
+            self._check(self.L.hj_accel_build_async(self.ctx, p(xf), p(ixf), self.scene.n_instances, mode), "hj_accel_build_async")
+
+    def accel_wait(self):
+        self._check(self.L.hj_accel_wait(self.ctx), "hj_accel_wait")
 
     def render(self, fparams, sync=True):
         self.fp = fparams

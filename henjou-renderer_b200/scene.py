@@ -134,6 +134,13 @@ class SceneData:
     def set_sky(self, rgb):
         self.ibl = np.array([[[rgb[0], rgb[1], rgb[2], 0.0]]], np.float32)   # texture.h:58-65
 
+    def set_sky_image(self, rgb):
+        """Equirect sky image float[H,W,3] (or [H,W,4]) -> the float4 image of HDRTexture, w = 0 (texture.h:67-101)."""
+        rgb = np.asarray(rgb, np.float32)
+        img = np.zeros(rgb.shape[:2] + (4,), np.float32)
+        img[..., :3] = rgb[..., :3]
+        self.ibl = img
+
     def transforms(self, time=None):
         """Per-instance row-major 3x4 matrices and the rows of their inverses (renderer.h:257-291).
         time=None -> identity (cpySceneDataToDevice, renderer.h:197-255)."""

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define HJ_ABI_VERSION 2
+#define HJ_ABI_VERSION 3
 
 typedef struct hj_ctx hj_ctx;
 
@@ -96,8 +96,9 @@ typedef struct hj_texture {
 /* The nine SceneData arrays (include/renderer/scene.h:19-37) + materials, textures, sky and LUT. */
 typedef struct hj_scene_desc {
     const float* vertices;            /* float3[n_vertices], object space                          */
-    const float* normals;             /* float3[n_vertices]                                        */
-    const float* texcoords;           /* float2[n_vertices]                                        */
+    const float* normals;             /* float3[n_vertices]; NULL: (0,1,0) everywhere — the reference LOADER substitutes geometric normals
+                                         (gltfloader.h:1460-1482), a host that relies on that must compute them before the call   */
+    const float* texcoords;           /* float2[n_vertices]; NULL: (0,0) everywhere (gltfloader.h:1476-1482)                        */
     const uint32_t* indices;          /* uint32[3*n_triangles] (loader emits the identity)         */
     const uint32_t* material_ids;     /* uint32[n_triangles]                                       */
     const uint32_t* prim_offsets;     /* uint32[n_instances], first global triangle of instance i  */
@@ -181,6 +182,16 @@ int hj_scene_upload(hj_ctx* ctx, const hj_scene_desc* scene);
  * xforms3x4: n_instances row-major 3x4 instance-to-world matrices (Matrix4x3, include/cu/matrix_4x3.h:12);
  * inv_xforms3x4: rows of the inverse (renderer.h:272-284), NULL = computed here. NULL xforms = identity. */
 int hj_accel_build(hj_ctx* ctx, const float* xforms3x4, const float* inv_xforms3x4, uint32_t n_instances, int mode);
+
+/* The same build, enqueued on the context's low-priority build stream without a single host synchronisation (PLOC rounds and
+ * collapse levels are driven from the device). It fills the second set of acceleration buffers while a frame enqueued by
+ * hj_render_async reads the first, i.e. frame N+1's update runs under frame N's shading — what the reference's frame loop does
+ * with updateIASMatrix (renderer.h:1126-1133, 257-291) minus its stall. The next hj_render / hj_render_async / hj_trace (or
+ * hj_accel_wait) waits for it, validates it and switches to the new buffers; a failed build leaves the previous structure in place
+ * and is reported there. The matrices are copied before the call returns. At most one build is in flight: a second call first
+ * completes the pending one. */
+int hj_accel_build_async(hj_ctx* ctx, const float* xforms3x4, const float* inv_xforms3x4, uint32_t n_instances, int mode);
+int hj_accel_wait(hj_ctx* ctx);
 
 /* ≙ cudaMemcpy(Params) + optixLaunch + CUDA_SYNC_CHECK (renderer.h:1229-1242). Synchronous. */
 int hj_render(hj_ctx* ctx, const hj_frame_params* frame);

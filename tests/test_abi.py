@@ -26,7 +26,7 @@ def test_exports_match_header(lib):
     assert declared == set(abi.EXPORTS), declared ^ set(abi.EXPORTS)
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.hj_abi_version() == 2
+    assert lib.hj_abi_version() == 3
 
 
 def test_struct_sizes():

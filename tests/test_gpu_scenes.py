@@ -160,3 +160,92 @@ def test_mis_emitter_first_query_is_the_closest_hit_query(gpu, which):
     gpu.build_accel(mode=abi.ACCEL_REFIT)
     gpu.render(fp)
     assert np.array_equal(gpu.readback(abi.AOV_ACCUM).view(np.uint32), out[0].view(np.uint32))
+
+
+@pytest.mark.parametrize("integrator", [abi.INTEGRATOR_PT, abi.INTEGRATOR_NEE, abi.INTEGRATOR_MIS])
+def test_equirect_sky_image(gpu, integrator):
+    """The miss program's equirect lookup (u = atan2(z,x)/2pi, v = acos(y)/pi, bilinear, wrap; setSky renderer.h:802-851)
+    with a NON-constant sky image — round 1 only ever rendered 1x1 skies. A seeded 64x32 image with a 40x 'sun', intensity 0.75:
+    a rough metal sphere and a diffuse floor under it (every miss goes through atan2f / acosf of hj_libm), and the Cornell box,
+    whose open side lets rays escape. Per path the same bits as the oracle."""
+    from henjou_renderer_b200 import hdrio
+    sky = hdrio.rgbe_to_float4(hdrio.float_to_rgbe(hdrio.procedural_sky(64, 32, seed=4)))      # what the .hdr loader would deliver
+    assert sky.max() > 20 and sky[..., :3].min() >= 0
+    s = scenes.furnace_sphere(metallic=1.0, roughness=0.35, subdiv=3)
+    s.set_sky_image(sky)
+    fp = hj.frame_params(s, 96, 96, 3, frame=2, max_depth=8, integrator=integrator, ibl_intensity=0.75, debug_paths=1)
+    gpu.upload(s); gpu.build_accel(); gpu.render(fp)
+    want = Oracle(s).render(fp, debug=True)
+    pt.compare_paths("equirect sky 64x32, metal sphere, integrator %d" % integrator, gpu.readback(abi.AOV_PATH_RADIANCE), gpu.readback(abi.AOV_PATH_IDS), want, exact=True)
+    assert pt.bit_equal(gpu.readback(abi.AOV_COLOR), want["color"])
+    miss = want["path_ids"][..., 0] == 0xffffffff
+    assert miss.mean() > 0.25 and np.unique(want["path_radiance"][miss][:, 0]).size > 50      # primary misses see many different texels
+    import os
+    c = hj.load_npz(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "cornelbox.npz"))
+    c.set_sky_image(sky)
+    xf, inv = c.transforms(1 / 24)
+    fp = hj.frame_params(c, 80, 80, 2, frame=1, max_depth=8, integrator=integrator, ibl_intensity=0.75, debug_paths=1)
+    gpu.upload(c); gpu.build_accel(xf, inv); gpu.render(fp)
+    want = Oracle(c, xforms=xf, inv_xforms=inv).render(fp, debug=True)
+    pt.compare_paths("equirect sky 64x32, cornell box, integrator %d" % integrator, gpu.readback(abi.AOV_PATH_RADIANCE), gpu.readback(abi.AOV_PATH_IDS), want, exact=True)
+
+
+def test_nonfinite_vertex_is_an_error_not_a_hang(gpu):
+    """one NaN / inf vertex makes a cluster that can never merge (every merged area is NaN). Round 1's single-block PLOC
+    tail then spun for ever. Now k_flatten flags non-finite world positions, both PLOC kernels stop when a round merges nothing, and
+    hj_accel_build reports it."""
+    import copy, os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    good = hj.load_npz(os.path.join(root, "tests", "golden", "cornelbox.npz"))
+    for bad_value in (np.nan, np.inf):
+        s = copy.copy(good)
+        s.vertices = good.vertices.copy(); s.vertices[100, 1] = bad_value
+        gpu.upload(s)
+        for builder in (1, 0):
+            gpu.set_option("builder", builder)
+            with pytest.raises(hj.HenjouError, match="not finite"):
+                gpu.build_accel()
+        gpu.set_option("builder", 1)
+    # a NaN in the instance matrices too
+    gpu.upload(good)
+    xf, inv = good.transforms(0.0)
+    xf = xf.copy(); xf[1, 0, 3] = np.nan
+    with pytest.raises(hj.HenjouError, match="not finite"):
+        gpu.build_accel(xf, inv)
+    gpu.build_accel(*good.transforms(0.0))                     # and the context is still usable
+    gpu.render(hj.frame_params(good, 32, 32, 1))
+    assert np.isfinite(gpu.readback(abi.AOV_COLOR)).all()
+
+
+def test_async_accel_update_under_a_frame_in_flight(gpu):
+    """hj_accel_build_async builds frame N+1's structure into the second buffer set on the build stream while frame N
+    (enqueued with hj_render_async) is still being shaded; the next render switches to it. Every frame must be bit-identical to the
+    blocking sequence (build -> render -> read back), for rebuild and for refit."""
+    s = scenes.rtcamp_like(statue_subdiv=4, detail=0.08, animated=8)
+    gpu.upload(s)
+    frames = list(range(0, 6))
+    fps = [hj.frame_params(s, 160, 90, 2, frame=f, max_depth=6, debug_paths=1) for f in frames]
+    want = []
+    for f, fp in zip(frames, fps):                             # blocking reference sequence
+        gpu.build_accel(*s.transforms(f / 24.0), mode=abi.ACCEL_BUILD)
+        gpu.render(fp)
+        want.append([gpu.readback(a).copy() for a in (abi.AOV_ACCUM, abi.AOV_PATH_RADIANCE, abi.AOV_PATH_IDS, abi.AOV_RGBA8)])
+    for mode in (abi.ACCEL_BUILD, abi.ACCEL_REFIT):
+        gpu.build_accel(*s.transforms(frames[0] / 24.0), mode=abi.ACCEL_BUILD)
+        for k, (f, fp) in enumerate(zip(frames, fps)):
+            gpu.render(fp, sync=False)                         # frame f in flight ...
+            if k + 1 < len(frames):
+                gpu.build_accel(*s.transforms(frames[k + 1] / 24.0), mode=mode, sync=False)   # ... while f+1's structure is built
+            gpu.sync()
+            got = [gpu.readback(a).copy() for a in (abi.AOV_ACCUM, abi.AOV_PATH_RADIANCE, abi.AOV_PATH_IDS, abi.AOV_RGBA8)]
+            for a, b in zip(got, want[k]):
+                assert pt.bit_equal(a, b), (mode, f)
+    # accel_wait reports a failed asynchronous build; the previous structure stays in place
+    xf, inv = s.transforms(0.0)
+    bad = xf.copy(); bad[0, 0, 0] = np.inf
+    gpu.build_accel(bad, inv, sync=False)
+    with pytest.raises(hj.HenjouError, match="not finite"):
+        gpu.accel_wait()
+    gpu.render(fps[-1])
+    assert pt.bit_equal(gpu.readback(abi.AOV_ACCUM), want[-1][0])
+    assert gpu.stats()["ms_accel"] > 0

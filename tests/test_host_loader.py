@@ -142,3 +142,30 @@ def test_bad_inputs_fail_loudly(tmp_path):
     (tmp_path / "render_option.json").write_text('{"Image": {"image_width": 4}}')
     r = subprocess.run([CLI, "render_option.json", "--dump-scene", "x.bin"], cwd=str(tmp_path), capture_output=True, text=True)
     assert r.returncode == 1 and "missing key" in r.stderr
+
+
+@pytest.mark.parametrize("rle", [True, False])
+def test_hdr_sky_through_the_cpp_host(tmp_path, rle):
+    """Sky.use_IBL: a Radiance .hdr (new-style RLE and flat scanlines) written by the Python mirror, read by host/hj_hdr.h through the
+    CLI: the float4 sky image must be rgb * 2^(e-136), w = 0 (stb_image's decode, texture.h:67-101), bit for bit."""
+    from henjou_renderer_b200 import hdrio
+    scene = hj.load_npz(os.path.join(ROOT, "tests", "golden", "cornelbox.npz"))
+    npz_to_gltf.export_gltf(scene, str(tmp_path / "Model"), "c")
+    sky = hdrio.procedural_sky(64, 32, seed=4)
+    sky[5, 8:40] = sky[5, 8]                                  # a long constant run for the RLE coder
+    os.makedirs(str(tmp_path / "HDRI"))
+    rgbe = hdrio.write_hdr(str(tmp_path / "HDRI" / "sky.hdr"), sky, rle=rle)
+    npz_to_gltf.write_render_option(str(tmp_path / "render_option.json"), "./Model/", "c.gltf", "out", 32, 32, 1, ibl_path="./HDRI/sky.hdr", ibl_intensity=0.75)
+    run_cli(["render_option.json", "--dump-scene", "scene.bin", "--quiet"], str(tmp_path))
+    dump = read_dump(str(tmp_path / "scene.bin"))
+    want = hdrio.rgbe_to_float4(rgbe)
+    assert dump["ibl"].size == 64 * 32 * 4
+    assert np.array_equal(dump["ibl"].view(np.uint32), want.reshape(-1).view(np.uint32))
+    assert (np.abs(want[..., :3] - sky) <= sky.max(-1, keepdims=True) / 128 + 1e-6).all() and (want[..., 3] == 0).all()   # RGBE: 8 bits of the largest component
+    assert dump["options"][6] == np.float32(0.75)
+    if rle:
+        assert os.path.getsize(str(tmp_path / "HDRI" / "sky.hdr")) < 64 * 32 * 4 + 60             # the runs really are coded
+    # a missing file falls back to the constant default sky (texture.h:91-101)
+    npz_to_gltf.write_render_option(str(tmp_path / "render_option.json"), "./Model/", "c.gltf", "out", 32, 32, 1, ibl_path="./HDRI/absent.hdr", sky=(0.1, 0.2, 0.3))
+    run_cli(["render_option.json", "--dump-scene", "scene.bin", "--quiet"], str(tmp_path))
+    assert np.array_equal(read_dump(str(tmp_path / "scene.bin"))["ibl"], np.array([0.1, 0.2, 0.3, 0.0], np.float32))

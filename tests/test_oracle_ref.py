@@ -67,6 +67,19 @@ def test_c3_standin_metaglass_matches_reference_headers():
     _assert_bridge(*_pair(s, fparams))
 
 
+def test_equirect_sky_image_matches_reference_headers():
+    """The reconstructed miss program with a non-constant sky image: the lookup itself has no reference source, but every
+    radiance it returns flows through the reference's integrators — frames still agree bit for bit."""
+    from henjou_renderer_b200 import hdrio
+    s = scenes.furnace_sphere(metallic=1.0, roughness=0.35, subdiv=3)
+    s.set_sky_image(hdrio.rgbe_to_float4(hdrio.float_to_rgbe(hdrio.procedural_sky(64, 32, seed=4))))
+    for integ in (abi.INTEGRATOR_PT, abi.INTEGRATOR_MIS):
+        fparams = hj.frame_params(s, 48, 48, 2, frame=2, max_depth=10, integrator=integ, ibl_intensity=0.75)
+        a, b = _pair(s, fparams)
+        _assert_bridge(a, b)
+        assert np.unique(a["color"][..., 0]).size > 500
+
+
 @pytest.mark.parametrize("which", ["cornell", "c2"])
 def test_shared_libm_build_against_glibc_build(cornell, which):
     """The only link of the chain that is not exact. Measured on larger frames by tools/parity_margins.py

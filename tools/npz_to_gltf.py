@@ -190,7 +190,7 @@ def export_gltf(scene, out_dir, name, fov_fallback=None):
 
 def write_render_option(path, gltf_dir, gltf_name, image_name, width, height, spp, sky=(0.8, 0.8, 0.8), fps=24, start_frame=1,
                         end_frame=2, camera_position=(0, 1, -7), camera_direction=(0, 0, 1), camera_fov=45.0, lut_path="./LUT/Thin_Film_LUT.png",
-                        allow_camera_animation=True, integrator=None, render_mode="Default", time_limit=5.0):
+                        allow_camera_animation=True, integrator=None, render_mode="Default", time_limit=5.0, ibl_path=None, ibl_intensity=1.0):
     """A render_option.json with the reference's schema (HenjouRenderer/render_option.json)."""
     j = dict(Image=dict(image_width=width, image_height=height, image_name=image_name, image_directory="./", max_spp=spp),
              Render_mode=render_mode, GLTF_file=dict(gltf_filepath=gltf_dir, gltf_filename=gltf_name),
@@ -198,7 +198,7 @@ def write_render_option(path, gltf_dir, gltf_name, image_name, width, height, sp
                          camera_direction=list(camera_direction), camera_fov=camera_fov),
              PTX_File=dict(ptxfile_path="../lib/ptx/Release/HenjouRenderer_generated_henjouRendererCU.cu.optixir"),
              Animation=dict(fps=fps, start_frame=start_frame, end_frame=end_frame, time_limit=time_limit),
-             Sky=dict(IBL_path="./HDRI/none.hdr", IBL_intensity=1.0, use_IBL=False, scene_sky_default=list(sky)),
+             Sky=dict(IBL_path=ibl_path or "./HDRI/none.hdr", IBL_intensity=ibl_intensity, use_IBL=ibl_path is not None, scene_sky_default=list(sky)),
              Option=dict(use_date=True, save_renderOption=False), LUT=dict(LUT_path=lut_path))
     if integrator:
         j["Integrator"] = integrator

@@ -36,13 +36,22 @@ r.pin(rgba)
 def run_sequence(spp, policy):
     """-> per-frame dicts (wall ms of update+render+read-back, device ms of the accel update and the render)"""
     out = []
+    overlapped = policy.endswith("_async")                 # next frame's update enqueued under this frame's shading (hj_accel_build_async)
+    if overlapped:
+        r.build_accel(*scene.transforms(0.0), mode=abi.ACCEL_BUILD)
     for f in range(frames):
-        xf, inv = scene.transforms(f / fps)
         fp = hj.frame_params(scene, W, H, spp, frame=f, max_depth=10)
         t0 = time.perf_counter()
-        mode = abi.ACCEL_BUILD if (policy == "rebuild" or f == 0) else abi.ACCEL_REFIT
-        r.build_accel(xf, inv, mode=mode)
-        r.render(fp)
+        if overlapped:
+            r.render(fp, sync=False)
+            if f + 1 < frames:
+                r.build_accel(*scene.transforms((f + 1) / fps), mode=abi.ACCEL_BUILD if policy == "rebuild_async" else abi.ACCEL_REFIT, sync=False)
+            r.sync()
+        else:
+            xf, inv = scene.transforms(f / fps)
+            mode = abi.ACCEL_BUILD if (policy == "rebuild" or f == 0) else abi.ACCEL_REFIT
+            r.build_accel(xf, inv, mode=mode)
+            r.render(fp)
         r.readback(abi.AOV_RGBA8, out=rgba)
         wall = (time.perf_counter() - t0) * 1e3
         st = r.stats()
@@ -64,10 +73,10 @@ def summary(rows):
 run_sequence(1, "rebuild")                               # warm-up (allocations, NCCL-free)
 if opts.get("spp", "auto") == "auto":
     # largest spp whose slowest frame fits the budget: time 2 spp, extrapolate, verify, step down if needed
-    probe = summary(run_sequence(2, "refit"))
+    probe = summary(run_sequence(2, "refit_async"))
     per_spp = max(probe["render_ms_mean"] / 2.0, 1e-3)
     spp = max(1, int((budget_ms - probe["accel_ms_mean"] - 2.0) / per_spp))
-    fits = lambda n: summary(run_sequence(n, "refit"))["frames_over_budget"] == 0
+    fits = lambda n: summary(run_sequence(n, "refit_async"))["frames_over_budget"] == 0
     while spp > 1 and not fits(spp):
         spp -= 1
     while spp < 64 and fits(spp + 1):                    # the 2-spp probe overestimates the cost per sample: try upwards too
@@ -77,12 +86,13 @@ else:
 
 res = {}
 checks = {}
-for policy in ("rebuild", "refit"):
+for policy in ("rebuild", "refit", "rebuild_async", "refit_async"):
     rows = run_sequence(spp, policy)
     res[policy] = summary(rows)
     checks[policy] = [x["checksum"] for x in rows]
 # refit keeps frame 0's topology: traversal order differs, the closest-hit rule does not -> identical frames
 res["frames_identical_rebuild_vs_refit"] = checks["rebuild"] == checks["refit"]
+res["frames_identical_blocking_vs_async"] = checks["rebuild"] == checks["rebuild_async"] == checks["refit_async"]
 line = dict(workload="C4 rtcamp-like stand-in, %d rigidly animated instances, %d frames at %g fps, %dx%d, MIS, depth 10"
             % (animated, frames, fps, W, H), triangles=scene.n_triangles, budget_ms=round(budget_ms, 3), spp=spp, **res)
 print(json.dumps(line))
