@@ -67,10 +67,11 @@ int hj_comm_reduce(hj_ctx* c) {
     if (!c) return HJ_ERR_INVALID;
     if (!c->have_frame) { c->err = "hj_comm_reduce: nothing rendered yet"; return HJ_ERR_NO_FRAME; }
     HJ_CUDA(c, cudaSetDevice(c->device));
-    if (c->comm && c->nranks > 1) {
+    if (c->comm && c->nranks > 1 && !c->frame_reduced) {    // in place: summing twice would scale the frame by nranks
         const size_t count = 4 * (size_t)c->fp.width * c->fp.height;
         ncclResult_t r = c->nccl->AllReduce(c->aov_accum.p, c->aov_accum.p, count, ncclFloat32, ncclSum, (ncclComm_t)c->comm, c->stream);
         if (r != ncclSuccess) { c->err = std::string("ncclAllReduce: ") + (c->nccl->GetErrorString ? c->nccl->GetErrorString(r) : "error"); return HJ_ERR_COMM; }
+        c->frame_reduced = true;
     }
     int rc = hj_wavefront_finalize(c);
     if (rc) return rc;

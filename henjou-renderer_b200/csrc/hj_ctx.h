@@ -107,6 +107,7 @@ struct hj_ctx {
     std::vector<cudaEvent_t> ev_pool; std::vector<int> ev_kind;
     // multi-GPU
     NcclApi* nccl = nullptr; void* comm = nullptr; int rank = 0, nranks = 1;
+    bool frame_reduced = false;   // hj_comm_reduce already summed this frame's accumulation buffer (a second call only re-finalizes)
 };
 
 #define HJ_CUDA(ctx, call)                                                                         \

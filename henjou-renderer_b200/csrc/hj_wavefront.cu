@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(WF_THREADS) k_raygen(FrameK F, WfPtrs P, uint3
         P.thr[slot] = f4(thr, 0.0f); P.L[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         P.rng[slot] = st.depth;
         if (F.debug) P.dbg[slot] = make_uint2(0xffffffffu, 0x811c9dc5u);
-        if (s == 0) { P.aov_albedo[pix] = make_float4(0, 0, 0, 1); P.aov_normal[pix] = make_float4(0, 0, 0, 1); }
+        if (s == F.sample_begin) { P.aov_albedo[pix] = make_float4(0, 0, 0, 1); P.aov_normal[pix] = make_float4(0, 0, 0, 1); }   // guides: first sample of this context's slice (sample 0 on one GPU)
         // every first-iteration roulette passes (throughput 1 > any draw), so the queue is the identity
         P.q_ext[0][slot] = alive ? slot : 0xffffffffu;
     }
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SURF_MINB) k_surface(DevScene S
             const float4 hq = P.hit[slot];
             const uint32_t prim = __float_as_uint(hq.w);
             const uint32_t pix = F.pix0 + slot % F.npix;
-            const bool first_sample = (depth == 0 && s0 + slot / F.npix == 0);
+            const bool first_sample = (depth == 0 && s0 + slot / F.npix == F.sample_begin);
             if (prim == 0xffffffffu) {                               // __miss__ms (D6); AOVs stay 0 (raygen wrote them)
                 if (INTEG == HJ_INTEGRATOR_PT || depth == 0) {
                     const float3 em = sky_radiance(S, f3(P.ray_d[slot]), F.ibl);
@@ -704,7 +704,7 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     HJ_CUDA(c, cudaEventRecord(c->ev1, st));
     if (c->accel[c->accel_cur].ev_last_read) HJ_CUDA(c, cudaEventRecord(c->accel[c->accel_cur].ev_last_read, st));   // a later build into this set waits for this frame
     HJ_CUDA(c, cudaGetLastError());
-    c->fp = *fp; c->have_frame = true; c->have_output = false;
+    c->fp = *fp; c->have_frame = true; c->have_output = false; c->frame_reduced = false;
     c->stats.kernel_launches = launches;
     c->stats.paths = (uint64_t)ns * WH;
     c->stats.passes = n_passes;

@@ -92,6 +92,11 @@ inline Accessor accessor(const Json& g, const std::vector<std::vector<uint8_t>>&
     r.ptr = buf.data() + off;
     return r;
 }
+// the loader reads POSITION / NORMAL / TEXCOORD_0 / sampler data as 32-bit floats (tinygltf hands the reference raw bytes that it casts to
+// float*, gltfloader.h:1425-1482,1555-1590): anything else would be read past the range accessor() validated
+inline void require_float(const Accessor& a, int ncomp, const char* what) {
+    if (a.comp_type != 5126 || a.ncomp != ncomp) throw std::runtime_error(std::string("gltf: ") + what + " must be FLOAT with " + std::to_string(ncomp) + " component(s)");
+}
 inline float get_f(const Accessor& a, size_t i, int c) { float v; memcpy(&v, a.ptr + i * a.stride + 4 * (size_t)c, 4); return v; }
 inline uint32_t get_index(const Accessor& a, size_t i) {
     const uint8_t* p = a.ptr + i * a.stride;
@@ -174,6 +179,13 @@ inline void load_gltf(const std::string& dir, const std::string& name, RenderOpt
         for (int k = 0; k < 4; k++) a.r_val.push_back(n.has("rotation") ? (float)n.at("rotation").at((size_t)k).number() : dr[k]);
         for (int k = 0; k < 3; k++) a.s_val.push_back(n.has("scale") ? (float)n.at("scale").at((size_t)k).number() : ds[k]);
         if (n.has("mesh")) {
+            {   // a mesh without a single triangle would give an empty [prim_offset, next) range, which hj_scene_upload refuses for the whole
+                // scene ("strictly increasing"): such a node contributes no instance
+                size_t tris = 0;
+                for (const Json& prim : g.at("meshes").at((size_t)n.at("mesh").number()).at("primitives").arr)
+                    tris += (size_t)g.at("accessors").at((size_t)prim.at("indices").number()).at("count").number() / 3;
+                if (tris == 0) continue;
+            }
             sc.prim_offsets.push_back((uint32_t)(sc.indices.size() / 3));
             sc.instance_node.push_back((uint32_t)ni);
             uint32_t prim_id = (uint32_t)(sc.vertices.size() / 9);
@@ -182,10 +194,12 @@ inline void load_gltf(const std::string& dir, const std::string& name, RenderOpt
                 const Accessor ia = accessor(g, buffers, (int)prim.at("indices").number());
                 const Json& at = prim.at("attributes");
                 const Accessor pa = accessor(g, buffers, (int)at.at("POSITION").number());
+                require_float(pa, 3, "POSITION");
+                if (ia.ncomp != 1 || ia.comp_type == 5126) throw std::runtime_error("gltf: indices must be an integer SCALAR accessor");
                 const bool has_n = at.has("NORMAL"), has_t = at.has("TEXCOORD_0");
                 Accessor na{}, ta{};
-                if (has_n) na = accessor(g, buffers, (int)at.at("NORMAL").number());
-                if (has_t) ta = accessor(g, buffers, (int)at.at("TEXCOORD_0").number());
+                if (has_n) { na = accessor(g, buffers, (int)at.at("NORMAL").number()); require_float(na, 3, "NORMAL"); if (na.count < pa.count) throw std::runtime_error("gltf: NORMAL shorter than POSITION"); }
+                if (has_t) { ta = accessor(g, buffers, (int)at.at("TEXCOORD_0").number()); require_float(ta, 2, "TEXCOORD_0"); if (ta.count < pa.count) throw std::runtime_error("gltf: TEXCOORD_0 shorter than POSITION"); }
                 const uint32_t mat = (uint32_t)prim.int_or("material", 0);
                 for (size_t t = 0; t < ia.count / 3; t++) {
                     uint32_t idx[3]; float v[3][3], nn[3][3], tc[3][2];
@@ -234,7 +248,10 @@ inline void load_gltf(const std::string& dir, const std::string& name, RenderOpt
                 const Json& tgt = ch.at(i).at("target");
                 NodeAnimation& a = sc.animations.at((size_t)tgt.at("node").number());
                 const std::string& path = tgt.at("path").string();
-                for (size_t k = 0; k < data.count; k++) {
+                require_float(keys, 1, "animation sampler input");
+                require_float(data, path == "rotation" ? 4 : 3, "animation sampler output");
+                const size_t n_keys = keys.count < data.count ? keys.count : data.count;     // never past the shorter of the two
+                for (size_t k = 0; k < n_keys; k++) {
                     const float key = get_f(keys, k, 0);
                     if (path == "translation") { for (int c = 0; c < 3; c++) a.t_val.push_back(get_f(data, k, c)); a.t_key.push_back(key); }
                     else if (path == "rotation") { for (int c = 0; c < 4; c++) a.r_val.push_back(get_f(data, k, c)); a.r_key.push_back(key); }

@@ -169,3 +169,42 @@ def test_hdr_sky_through_the_cpp_host(tmp_path, rle):
     npz_to_gltf.write_render_option(str(tmp_path / "render_option.json"), "./Model/", "c.gltf", "out", 32, 32, 1, ibl_path="./HDRI/absent.hdr", sky=(0.1, 0.2, 0.3))
     run_cli(["render_option.json", "--dump-scene", "scene.bin", "--quiet"], str(tmp_path))
     assert np.array_equal(read_dump(str(tmp_path / "scene.bin"))["ibl"], np.array([0.1, 0.2, 0.3, 0.0], np.float32))
+
+
+def test_loader_validates_accessor_shapes(tmp_path):
+    """a NORMAL / TEXCOORD_0 / POSITION accessor that is not FLOAT VECn, or animation keys shorter than their data, must be
+    refused (they would be read past the validated range); a mesh node without triangles is dropped instead of breaking the scene."""
+    import json
+    scene = hj.load_npz(os.path.join(ROOT, "tests", "golden", "cornelbox.npz"))
+    npz_to_gltf.export_gltf(scene, str(tmp_path / "Model"), "c")
+    npz_to_gltf.write_render_option(str(tmp_path / "render_option.json"), "./Model/", "c.gltf", "out", 32, 32, 1)
+    path = str(tmp_path / "Model" / "c.gltf")
+    good = json.load(open(path))
+    prim = good["meshes"][0]["primitives"][0]
+    for attr, field, value, msg in (("NORMAL", "componentType", 5123, "NORMAL must be FLOAT"), ("POSITION", "type", "VEC2", "POSITION must be FLOAT"),
+                                    ("TEXCOORD_0", "type", "VEC3", "TEXCOORD_0 must be FLOAT")):
+        g = json.loads(json.dumps(good))
+        if attr not in prim["attributes"]:
+            continue
+        g["accessors"][prim["attributes"][attr]][field] = value
+        json.dump(g, open(path, "w"))
+        r = subprocess.run([CLI, "render_option.json", "--dump-scene", "x.bin", "--quiet"], cwd=str(tmp_path), capture_output=True, text=True)
+        assert r.returncode == 1 and msg in r.stderr, (attr, r.stderr)
+    # a mesh whose only primitive has no triangles: the node contributes no instance, the rest of the scene loads
+    g = json.loads(json.dumps(good))
+    n_inst = sum(1 for n in g["nodes"] if "mesh" in n)
+    empty_acc = json.loads(json.dumps(g["accessors"][prim["indices"]])); empty_acc["count"] = 0
+    g["accessors"].append(empty_acc)
+    g["meshes"].append({"primitives": [{"attributes": dict(prim["attributes"]), "indices": len(g["accessors"]) - 1, "material": 0}]})
+    g["nodes"].insert(1, {"mesh": len(g["meshes"]) - 1, "name": "empty"})
+    if "scenes" in g:
+        g["scenes"][0]["nodes"] = list(range(len(g["nodes"])))
+    for a in g.get("animations", []):
+        for ch in a["channels"]:
+            if ch["target"]["node"] >= 1:
+                ch["target"]["node"] += 1
+    json.dump(g, open(path, "w"))
+    run_cli(["render_option.json", "--dump-scene", "scene.bin", "--quiet"], str(tmp_path))
+    dump = read_dump(str(tmp_path / "scene.bin"))
+    assert dump["prim_offsets"].size == n_inst and np.all(np.diff(dump["prim_offsets"].astype(np.int64)) > 0)
+    assert dump["indices"].size == scene.indices.size
