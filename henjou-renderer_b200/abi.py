@@ -51,7 +51,7 @@ class hj_frame_params(C.Structure):
         ("camera_up", C.c_float * 3), ("camera_right", C.c_float * 3),
         ("camera_f", C.c_float), ("ibl_intensity", C.c_float),
         ("integrator", C.c_int32), ("max_depth", C.c_int32), ("tonemap", C.c_int32),
-        ("pixel_jitter", C.c_int32), ("debug_paths", C.c_int32), ("reserved", C.c_int32),
+        ("pixel_jitter", C.c_int32), ("debug_paths", C.c_int32), ("sky_sampling", C.c_int32),
     ]
 
 

@@ -45,7 +45,7 @@ def camera_basis(position, direction, fov, animation=None, time=0.0):
 
 def frame_params(scene, width, height, spp, frame=0, fps=24, integrator=abi.INTEGRATOR_MIS, max_depth=10,
                  tonemap=abi.TONEMAP_NONE, pixel_jitter=1, debug_paths=0, ibl_intensity=1.0,
-                 sample_begin=0, sample_end=None, allow_camera_animation=True, camera=None):
+                 sample_begin=0, sample_end=None, allow_camera_animation=True, camera=None, sky_sampling=0):
     """hj_frame_params for frame index `frame` (time = frame/fps, renderer.h:1128; scramble = frame)."""
     cam = camera if camera is not None else scene.camera
     time = float(f32(frame) / f32(fps))
@@ -62,4 +62,5 @@ def frame_params(scene, width, height, spp, frame=0, fps=24, integrator=abi.INTE
     fp.ibl_intensity = ibl_intensity
     fp.integrator, fp.max_depth, fp.tonemap = integrator, max_depth, tonemap
     fp.pixel_jitter, fp.debug_paths = pixel_jitter, debug_paths
+    fp.sky_sampling = sky_sampling        # 0 = reference behaviour; 1 = light-sampled sky with MIS (extension, MIS integrator only)
     return fp

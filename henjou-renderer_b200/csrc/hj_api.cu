@@ -30,6 +30,25 @@ __global__ void k_tri_inst(const uint32_t* __restrict__ prim_offsets, uint32_t n
     tri_inst[t] = lo;
 }
 
+// Sky sampling table (frame parameter sky_sampling): row y, sequentially: running sum of luminance(texel) x sin(pi (y + 1/2) / H); then
+// the running sum of the row totals. One thread per row / one thread: the SAME float addition order as the oracle's loops.
+__global__ void k_sky_rows(const float4* __restrict__ ibl, int W, int H, float* __restrict__ row_cdf) {
+    const int y = blockIdx.x * blockDim.x + threadIdx.x;
+    if (y >= H) return;
+    const float st = hj_sinf(M_PIf * ((float)y + 0.5f) / (float)H);
+    float run = 0.0f;
+    for (int x = 0; x < W; x++) {
+        const float4 c = ibl[(size_t)y * W + x];
+        const float lum = 0.2126f * c.x + 0.7152f * c.y + 0.0722f * c.z;
+        run += fmaxf(lum, 0.0f) * st;
+        row_cdf[(size_t)y * W + x] = run;
+    }
+}
+__global__ void k_sky_marginal(const float* __restrict__ row_cdf, int W, int H, float* __restrict__ marg) {
+    float run = 0.0f;
+    for (int y = 0; y < H; y++) { run += row_cdf[(size_t)y * W + W - 1]; marg[y] = run; }
+}
+
 __global__ void k_libm_eval(int fn, const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out, uint64_t n) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -88,7 +107,7 @@ void hj_destroy(hj_ctx* c) {
     hj_comm_destroy_internal(c);
     DevBuf* bufs[] = {&c->d_vertices, &c->d_normals, &c->d_texcoords, &c->d_indices, &c->d_material_ids, &c->d_prim_offsets, &c->d_tri_inst,
                       &c->d_materials, &c->d_textures, &c->d_texels, &c->d_srgb, &c->d_light_ids, &c->d_light_em,
-                      &c->d_ibl, &c->d_lut,
+                      &c->d_ibl, &c->d_lut, &c->d_sky_rows, &c->d_sky_marg,
                       &c->bvh.keys, &c->bvh.keys_alt, &c->bvh.vals, &c->bvh.vals_alt, &c->bvh.block_hist, &c->bvh.digit_total, &c->bvh.status, &c->bvh.blo, &c->bvh.bhi, &c->bvh.left,
                       &c->bvh.right, &c->bvh.parent, &c->bvh.cnt, &c->bvh.flags, &c->bvh.p_cid[0], &c->bvh.p_cid[1], &c->bvh.p_lo[0], &c->bvh.p_lo[1],
                       &c->bvh.p_hi[0], &c->bvh.p_hi[1], &c->bvh.p_nn, &c->bvh.p_keep, &c->bvh.p_bcount, &c->bvh.bounds, &c->bvh.queue_a, &c->bvh.queue_b,
@@ -219,6 +238,9 @@ int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
     int iw = 1, ih = 1;
     if (d->ibl_rgba32f && d->ibl_width > 0 && d->ibl_height > 0) { iw = d->ibl_width; ih = d->ibl_height; if ((rc = upload(c, c->d_ibl, d->ibl_rgba32f, 4 * (size_t)iw * ih))) return rc; }
     else if ((rc = upload(c, c->d_ibl, black, (size_t)4))) return rc;
+    HJ_CUDA(c, c->d_sky_rows.reserve((size_t)iw * ih * 4)); HJ_CUDA(c, c->d_sky_marg.reserve((size_t)ih * 4));
+    k_sky_rows<<<(ih + 63) / 64, 64, 0, c->stream>>>(c->d_ibl.as<float4>(), iw, ih, c->d_sky_rows.as<float>());
+    k_sky_marginal<<<1, 1, 0, c->stream>>>(c->d_sky_rows.as<float>(), iw, ih, c->d_sky_marg.as<float>());
     const bool has_lut = d->lut_rgba8 && d->lut_width > 0 && d->lut_height > 0;
     if (has_lut) { if ((rc = upload(c, c->d_lut, d->lut_rgba8, 4 * (size_t)d->lut_width * d->lut_height))) return rc; }
     HJ_CUDA(c, cudaEventRecord(c->ev_scene, c->stream));
@@ -233,6 +255,7 @@ int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
     S.materials = c->d_materials.as<DevMaterial>(); S.textures = c->d_textures.as<DevTexture>(); S.srgb_table = c->d_srgb.as<float>();
     S.light_prim_ids = c->d_light_ids.as<uint32_t>(); S.light_prim_emission = c->d_light_em.as<float>();
     S.ibl = c->d_ibl.as<float4>(); S.ibl_w = iw; S.ibl_h = ih;
+    S.sky_row_cdf = c->d_sky_rows.as<float>(); S.sky_marg = c->d_sky_marg.as<float>();
     S.lut = c->d_lut.as<uchar4>(); S.lut_w = has_lut ? d->lut_width : 0; S.lut_h = has_lut ? d->lut_height : 0; S.has_lut = has_lut;
     c->have_scene = true;
     return HJ_OK;

@@ -66,9 +66,10 @@ struct WavefrontState {
     DevBuf q_extend[2], q_shadow, q_mis;                 // queues
     DevBuf q_cls[3], q_ns, sf[4];                        // shade stages: per-class queues, non-specular queue, surface records
     DevBuf sh_o, sh_d, sh_c;      // shadow ray payload per slot: origin+tmax, dir, contribution
+    DevBuf q_sky, sk_d, sk_c;     // sky-sample shadow rays (frame parameter sky_sampling): queue, direction, contribution
     DevBuf mi_o, mi_d, mi_a, mi_t;   // MIS ray payload per slot
     DevBuf counters;              // device-side queue counters + ray statistics
-    DevBuf* all[28] = {&ray_o, &ray_d, &hit, &thr, &L, &rng_depth, &dbg, &q_extend[0], &q_extend[1], &q_shadow, &q_mis,
+    DevBuf* all[31] = {&q_sky, &sk_d, &sk_c, &ray_o, &ray_d, &hit, &thr, &L, &rng_depth, &dbg, &q_extend[0], &q_extend[1], &q_shadow, &q_mis,
                        &sh_o, &sh_d, &sh_c, &mi_o, &mi_d, &mi_a, &mi_t, &counters, &q_cls[0], &q_cls[1], &q_cls[2], &q_ns,
                        &sf[0], &sf[1], &sf[2], &sf[3], nullptr};
 };
@@ -87,7 +88,7 @@ struct hj_ctx {
     bool have_scene = false, have_accel = false, have_frame = false;
     DevScene S{};                 // device pointers (host copy of the struct, passed to kernels by value)
     DevBuf d_vertices, d_normals, d_texcoords, d_indices, d_material_ids, d_prim_offsets, d_tri_inst;
-    DevBuf d_materials, d_textures, d_texels, d_srgb, d_light_ids, d_light_em, d_ibl, d_lut;
+    DevBuf d_materials, d_textures, d_texels, d_srgb, d_light_ids, d_light_em, d_ibl, d_lut, d_sky_rows, d_sky_marg;
     AccelSet accel[2]; int accel_cur = 0;      // S points into accel[accel_cur]
     BvhState bvh;
     WavefrontState wf[HJ_MAX_PIPES];

@@ -27,6 +27,9 @@ struct DevScene {
     const DevMaterial* materials; const DevTexture* textures; const float* srgb_table;
     const uint32_t* light_prim_ids; const float* light_prim_emission;
     const float4* ibl; int ibl_w, ibl_h;
+    // sky importance sampling (option, frame parameter sky_sampling): unnormalised running sums of luminance x sin(theta) per row,
+    // and of the row totals (built by k_sky_rows / k_sky_marginal at upload)
+    const float* sky_row_cdf; const float* sky_marg;
     const uchar4* lut; int lut_w, lut_h, has_lut;
     // world-space flattening, rebuilt by hj_accel_build (≙ updateIASMatrix, renderer.h:257-291)
     float4* tri_pos;     // 3 per triangle, by global primitive id
@@ -89,6 +92,54 @@ static HJ_NI float3 sky_radiance(const DevScene& S, const float3& dir, float ibl
         c = lerp4(top, bot, b);
     }
     return ibl_intensity * f3(c);
+}
+
+// ---- sky importance sampling (the reference BSDF-samples the sky only, rt.h:417-419 — this is an extension behind
+// hj_frame_params::sky_sampling; the CPU checker of the tests restates it operation for operation). Density on the unit (u, v) square:
+// piecewise constant per texel, proportional to luminance x sin(theta_row); solid-angle density = that / (2 pi^2 sin theta).
+HJ_DI float sky_texel_weight(const DevScene& S, int x, int y) {
+    const float* row = S.sky_row_cdf + (size_t)y * S.ibl_w;
+    return row[x] - (x ? row[x - 1] : 0.0f);
+}
+HJ_DI float sky_pdf_texel(const DevScene& S, int x, int y, float sin_theta) {
+    const float total = S.sky_marg[S.ibl_h - 1];
+    if (!(total > 0.0f) || !(sin_theta > 0.0f)) return 0.0f;
+    const float pdf_uv = sky_texel_weight(S, x, y) * (float)S.ibl_w * (float)S.ibl_h / total;
+    return pdf_uv / (2.0f * M_PIf * M_PIf * sin_theta);
+}
+// first index in [0, n) whose running sum exceeds t (the last one if none does)
+HJ_DI int sky_search(const float* cdf, int n, float t) {
+    int lo = 0, hi = n - 1;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (cdf[mid] > t) hi = mid; else lo = mid + 1; }
+    return lo;
+}
+static HJ_NI float3 sky_sample(const DevScene& S, const float2& xi, float& pdf) {
+    pdf = 0.0f;
+    const float total = S.sky_marg[S.ibl_h - 1];
+    if (!(total > 0.0f)) return f3(0.0f, 1.0f, 0.0f);
+    const float ty = xi.x * total;
+    const int y = sky_search(S.sky_marg, S.ibl_h, ty);
+    const float* row = S.sky_row_cdf + (size_t)y * S.ibl_w;
+    const float tx = xi.y * row[S.ibl_w - 1];
+    const int x = sky_search(row, S.ibl_w, tx);
+    const float px = x ? row[x - 1] : 0.0f, fx = row[x] - px;
+    const float py = y ? S.sky_marg[y - 1] : 0.0f, fy = S.sky_marg[y] - py;
+    const float du = fx > 0.0f ? clampf((tx - px) / fx, 0.0f, 0.99999994f) : 0.5f;
+    const float dv = fy > 0.0f ? clampf((ty - py) / fy, 0.0f, 0.99999994f) : 0.5f;
+    const float u = ((float)x + du) / (float)S.ibl_w, v = ((float)y + dv) / (float)S.ibl_h;
+    float sp, cp, st, ct;
+    hj_sincosf(2.0f * M_PIf * u, sp, cp); hj_sincosf(M_PIf * v, st, ct);
+    pdf = sky_pdf_texel(S, x, y, st);
+    return f3(st * cp, ct, st * sp);
+}
+static HJ_NI float sky_pdf(const DevScene& S, const float3& dir) {
+    float phi = hj_atan2f(dir.z, dir.x);
+    if (phi < 0.0f) phi += 2.0f * M_PIf;
+    const float theta = hj_acosf(clampf(dir.y, -1.0f, 1.0f));
+    const float u = phi * (1.0f / (2.0f * M_PIf)), v = theta * (1.0f / M_PIf);
+    int x = (int)(u * (float)S.ibl_w), y = (int)(v * (float)S.ibl_h);
+    x = x < 0 ? 0 : (x > S.ibl_w - 1 ? S.ibl_w - 1 : x); y = y < 0 ? 0 : (y > S.ibl_h - 1 ? S.ibl_h - 1 : y);
+    return sky_pdf_texel(S, x, y, hj_sinf(theta));
 }
 
 // disneyBRDF.h:11-14 — thin-film LUT: RGBA8, wrap, bilinear, non-sRGB

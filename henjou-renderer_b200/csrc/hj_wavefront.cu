@@ -20,10 +20,11 @@
 struct WfCounters {
     uint32_t n_extend[2]; uint32_t n_shadow, n_mis;
     uint32_t n_cls[3], n_ns;      // shade-stage queues: Disney / EC-GGX / glass surfaces, and all non-specular ones
-    uint32_t next[4];             // work-fetch cursors of the persistent traversal kernels (extend, shadow, mis)
+    uint32_t n_sky;               // sky-sample shadow rays (sky_sampling)
+    uint32_t next[4];             // work-fetch cursors of the persistent traversal kernels (extend, shadow, mis, sky)
     unsigned long long rays_extend, rays_shadow, nodes, tris;
     uint32_t max_nodes, max_tris;
-    unsigned long long diag[3][8];   // count_fetches: lane-state census of the traversal loop per ray type
+    unsigned long long diag[4][8];   // count_fetches: lane-state census of the traversal loop per ray type
 };
 
 struct FrameK {
@@ -31,6 +32,7 @@ struct FrameK {
     uint32_t pix0, npix;      // this pass covers pixels [pix0, pix0 + npix) of its samples: slot = s_local * npix + (pixel - pix0)
     float3 cpos, cdir, cup, cright; float cf, ibl;
     int integrator, max_depth, tonemap, jitter, debug;
+    int sky;                  // hj_frame_params::sky_sampling (MIS only): light-sampled sky with MIS, an extension over the reference
 };
 
 struct WfPtrs {
@@ -38,6 +40,7 @@ struct WfPtrs {
     uint32_t *q_ext[2], *q_shadow, *q_mis, *q_cls[3], *q_ns;
     float4 *sf0, *sf1, *sf2, *sf3;   // surface record per slot: (pos, roughness) (normal, metallic) (basecolor, sheen) (clearcoat, ior, flags, -)
     float4 *sh_o, *sh_d, *sh_c, *mi_o, *mi_d, *mi_a, *mi_t;
+    uint32_t* q_sky; float4 *sk_d, *sk_c;
     WfCounters* cnt;
     float4 *aov_albedo, *aov_normal;
 };
@@ -218,7 +221,7 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_NEE_MINB) k_nee(DevScene S, Fra
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
         const uint32_t slot = (i < n) ? P.q_ns[i] : 0xffffffffu;
-        bool push_shadow = false;
+        bool push_shadow = false, push_sky = false;
         if (slot != 0xffffffffu) {
             const Surface prd = load_surface(P, slot);
             const float3 d = f3(P.ray_d[slot]), thr = f3(P.thr[slot]);
@@ -227,27 +230,45 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_NEE_MINB) k_nee(DevScene S, Fra
             float3 t, b; const float3 nrm = prd.normal;
             onb(nrm, t, b);
             const float3 lwo = to_local(-d, t, nrm, b);
-            float lpdf; float3 lnrm, lem;
-            const float3 lpos = sample_light(S, st, lpdf, lnrm, lem);
-            float3 ld = lpos - prd.position;
-            const float dist = length(ld);
-            ld = normalize(ld);
-            const float c1 = absdot(nrm, ld), c2 = absdot(lnrm, -ld);
-            const float3 lwi = to_local(ld, t, nrm, b);
-            const float3 f = bsdf.eval(S, lwo, lwi);
-            const float G = c2 / (dist * dist);
-            float3 contrib;
-            if (INTEG == HJ_INTEGRATOR_MIS) {
-                const float ppdf = bsdf.pdf(lwo, lwi) * G;
-                const float w = lpdf / (lpdf + ppdf);
-                contrib = thr * (f * G * c1 / lpdf) * w * lem;
-            } else contrib = thr * (f * G * c1 / lpdf) * lem;
-            if (!is_zero3(contrib)) {
-                push_shadow = true;
-                P.sh_o[slot] = f4(prd.position, dist - 0.001f); P.sh_d[slot] = f4(ld, 0.0f); P.sh_c[slot] = f4(contrib, 0.0f);
+            if (S.n_lights >= 1) {
+                float lpdf; float3 lnrm, lem;
+                const float3 lpos = sample_light(S, st, lpdf, lnrm, lem);
+                float3 ld = lpos - prd.position;
+                const float dist = length(ld);
+                ld = normalize(ld);
+                const float c1 = absdot(nrm, ld), c2 = absdot(lnrm, -ld);
+                const float3 lwi = to_local(ld, t, nrm, b);
+                const float3 f = bsdf.eval(S, lwo, lwi);
+                const float G = c2 / (dist * dist);
+                float3 contrib;
+                if (INTEG == HJ_INTEGRATOR_MIS) {
+                    const float ppdf = bsdf.pdf(lwo, lwi) * G;
+                    const float w = lpdf / (lpdf + ppdf);
+                    contrib = thr * (f * G * c1 / lpdf) * w * lem;
+                } else contrib = thr * (f * G * c1 / lpdf) * lem;
+                if (!is_zero3(contrib)) {
+                    push_shadow = true;
+                    P.sh_o[slot] = f4(prd.position, dist - 0.001f); P.sh_d[slot] = f4(ld, 0.0f); P.sh_c[slot] = f4(contrib, 0.0f);
+                }
+            }
+            if (INTEG == HJ_INTEGRATOR_MIS && F.sky) {
+                // extension (sky_sampling): one direction drawn from the sky's luminance table, balance heuristic against the BSDF
+                // pdf; the matching weight on BSDF-sampled rays that reach the sky is applied in finish_mis
+                const float2 xi = draw2(st);
+                float spdf;
+                const float3 sd = sky_sample(S, xi, spdf);
+                if (spdf > 0.0f) {
+                    const float c1 = absdot(nrm, sd);
+                    const float3 lwi = to_local(sd, t, nrm, b);
+                    const float3 f = bsdf.eval(S, lwo, lwi);
+                    const float w = spdf / (spdf + bsdf.pdf(lwo, lwi));
+                    const float3 contrib = thr * (f * c1 / spdf) * w * sky_radiance(S, sd, F.ibl);
+                    if (!is_zero3(contrib)) { push_sky = true; P.sk_d[slot] = f4(sd, 0.0f); P.sk_c[slot] = f4(contrib, 0.0f); }
+                }
             }
         }
         queue_push(&P.cnt->n_shadow, P.q_shadow, push_shadow, slot);
+        if (INTEG == HJ_INTEGRATOR_MIS && F.sky) queue_push(&P.cnt->n_sky, P.q_sky, push_sky, slot);
     }
 }
 
@@ -275,6 +296,7 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S
             float3 thr = f3(P.thr[slot]);
             Sampler st; st.n_spp = s0 + slot / F.npix; st.scramble = F.frame; st.image_idx = F.pix0 + slot % F.npix; st.depth = P.rng[slot];
             if (INTEG != HJ_INTEGRATOR_PT && S.n_lights >= 1) st.depth += 2;     // light pick + barycentrics (light_sample.h:18,60)
+            if (INTEG == HJ_INTEGRATOR_MIS && F.sky) st.depth += 1;               // the sky sample's draw (k_nee)
             float3 t, b; const float3 nrm = prd.normal;
             onb(nrm, t, b);
             const float3 lwo = to_local(-d, t, nrm, b);
@@ -364,12 +386,25 @@ HJ_DI void finish_mis(const DevScene& S, const FrameK& F, const WfPtrs& P, uint3
         }
     } else {
         const float3 em = sky_radiance(S, wi, F.ibl);
-        L += thr * f * c1 * em / ppdf;
+        if (F.sky && aq.w == 0.0f) {                       // sky_sampling: balance heuristic against the sky's light-sampling pdf
+            const float w = ppdf / (ppdf + sky_pdf(S, wi));
+            L += thr * w * f * c1 * em / ppdf;
+        } else L += thr * f * c1 * em / ppdf;              // reference: the sky through the BSDF branch, unweighted (rt.h:417-419)
     }
     if (F.debug) { uint2 g = P.dbg[slot]; g.y = (g.y ^ (h.prim + 1u)) * 0x01000193u; P.dbg[slot] = g; }
     P.L[slot] = f4(L, Lq.w + 1.0f);
 }
 
+// the shadow ray of a sky sample (sky_sampling): unoccluded to infinity -> its contribution
+HJ_DI void finish_sky(const FrameK& F, const WfPtrs& P, uint32_t slot, const Hit& h) {
+    if (h.prim != 0xffffffffu && !F.debug) return;
+    float4 L = P.L[slot];
+    if (h.prim == 0xffffffffu) { const float4 c = P.sk_c[slot]; L.x += c.x; L.y += c.y; L.z += c.z; }
+    L.w += 1.0f;
+    P.L[slot] = L;
+}
+
+// MODE 4: shadow ray of a sky sample (any hit, origin = the surface position, no far limit).
 // MODE 0: extend (closest hit), 1: shadow (any hit), 2: MIS emitter ray (closest hit), 3: MIS emitter ray answered by the
 // emitter-first query (QUERY 2 of hj_trace.cuh: closest emitter, then any hit in front of it) — same contribution, and the
 // walk through the whole scene may stop at the first blocker instead of finding the nearest one.
@@ -380,39 +415,40 @@ struct WfRayIO {
     HJ_DI bool load(uint32_t idx, float3& o, float3& d, float& tmin, float& tmax) {
         slot = queue[idx];
         if (slot == 0xffffffffu) return false;
-        const float4 oq = MODE == 0 ? P.ray_o[slot] : (MODE == 1 ? P.sh_o[slot] : P.mi_o[slot]);
-        const float4 dq = MODE == 0 ? P.ray_d[slot] : (MODE == 1 ? P.sh_d[slot] : P.mi_d[slot]);
+        const float4 oq = MODE == 0 ? P.ray_o[slot] : (MODE == 1 ? P.sh_o[slot] : (MODE == 4 ? P.sf0[slot] : P.mi_o[slot]));
+        const float4 dq = MODE == 0 ? P.ray_d[slot] : (MODE == 1 ? P.sh_d[slot] : (MODE == 4 ? P.sk_d[slot] : P.mi_d[slot]));
         o = f3(oq); d = f3(dq); tmin = 0.001f; tmax = MODE == 1 ? oq.w : 1e16f;
         return true;
     }
     HJ_DI void finish(const Hit& h) {
         if (MODE == 0) finish_extend(F, P, slot, h);
         else if (MODE == 1) finish_shadow(F, P, slot, h);
+        else if (MODE == 4) finish_sky(F, P, slot, h);
         else finish_mis(S, F, P, slot, h);
     }
 };
 
 template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace(DevScene S, FrameK F, WfPtrs P, int cur) {
-    constexpr int QUERY = MODE == 1 ? 1 : (MODE == 3 ? 2 : 0), CTR = MODE == 3 ? 2 : MODE;
+    constexpr int QUERY = (MODE == 1 || MODE == 4) ? 1 : (MODE == 3 ? 2 : 0), CTR = MODE == 3 ? 2 : (MODE == 4 ? 3 : MODE);
     __shared__ TraceShared<QUERY> sh;
     uint2 l_stack[HJ_STACK];
-    const uint32_t n = MODE == 0 ? P.cnt->n_extend[cur] : (MODE == 1 ? P.cnt->n_shadow : P.cnt->n_mis);
-    WfRayIO<MODE> io{S, F, P, MODE == 0 ? P.q_ext[cur] : (MODE == 1 ? P.q_shadow : P.q_mis), 0u};
+    const uint32_t n = MODE == 0 ? P.cnt->n_extend[cur] : (MODE == 1 ? P.cnt->n_shadow : (MODE == 4 ? P.cnt->n_sky : P.cnt->n_mis));
+    WfRayIO<MODE> io{S, F, P, MODE == 0 ? P.q_ext[cur] : (MODE == 1 ? P.q_shadow : (MODE == 4 ? P.q_sky : P.q_mis)), 0u};
     uint32_t nr = 0, nn = 0, nt = 0;
     trace_warp_loop<QUERY, COUNT>(S, io, n, &P.cnt->next[CTR], sh, l_stack, nr, nn, nt, &P.cnt->max_nodes, &P.cnt->max_tris, P.cnt->diag[CTR]);
-    warp_add64(MODE == 1 ? &P.cnt->rays_shadow : &P.cnt->rays_extend, nr);
+    warp_add64((MODE == 1 || MODE == 4) ? &P.cnt->rays_shadow : &P.cnt->rays_extend, nr);
     if (COUNT) { warp_add64(&P.cnt->nodes, nn); warp_add64(&P.cnt->tris, nt); }
 }
 
 // ---------------------------------------------------------------------------------------------- accumulate / write-out
 __global__ void k_reset_queues(WfCounters* c, uint32_t n0, int all) {
     if (all) { c->n_extend[0] = n0; c->n_extend[1] = 0; }
-    c->n_shadow = 0; c->n_mis = 0; c->next[0] = c->next[1] = c->next[2] = 0;
+    c->n_shadow = 0; c->n_mis = 0; c->n_sky = 0; c->next[0] = c->next[1] = c->next[2] = c->next[3] = 0;
     c->n_cls[0] = c->n_cls[1] = c->n_cls[2] = c->n_ns = 0;
 }
 __global__ void k_swap_queues(WfCounters* c, int cur) {
-    c->n_extend[cur] = 0; c->n_shadow = 0; c->n_mis = 0; c->next[0] = c->next[1] = c->next[2] = 0;
+    c->n_extend[cur] = 0; c->n_shadow = 0; c->n_mis = 0; c->n_sky = 0; c->next[0] = c->next[1] = c->next[2] = c->next[3] = 0;
     c->n_cls[0] = c->n_cls[1] = c->n_cls[2] = c->n_ns = 0;
 }
 
@@ -500,7 +536,7 @@ int hj_trace_batch(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, u
 // ---------------------------------------------------------------------------------------------- host driver
 static inline uint32_t cdiv_u(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
 
-static int wf_reserve(hj_ctx* c, WavefrontState& w, uint32_t cap, bool mis, bool debug) {
+static int wf_reserve(hj_ctx* c, WavefrontState& w, uint32_t cap, bool mis, bool debug, bool sky) {
     const size_t f4s = (size_t)cap * sizeof(float4);
     HJ_CUDA(c, w.ray_o.reserve(f4s)); HJ_CUDA(c, w.ray_d.reserve(f4s)); HJ_CUDA(c, w.hit.reserve(f4s));
     HJ_CUDA(c, w.thr.reserve(f4s)); HJ_CUDA(c, w.L.reserve(f4s)); HJ_CUDA(c, w.rng_depth.reserve((size_t)cap * 4));
@@ -512,6 +548,7 @@ static int wf_reserve(hj_ctx* c, WavefrontState& w, uint32_t cap, bool mis, bool
     for (int k = 0; k < 4; k++) HJ_CUDA(c, w.sf[k].reserve(f4s));
     HJ_CUDA(c, w.sh_o.reserve(f4s)); HJ_CUDA(c, w.sh_d.reserve(f4s)); HJ_CUDA(c, w.sh_c.reserve(f4s));
     if (mis) { HJ_CUDA(c, w.mi_o.reserve(f4s)); HJ_CUDA(c, w.mi_d.reserve(f4s)); HJ_CUDA(c, w.mi_a.reserve(f4s)); HJ_CUDA(c, w.mi_t.reserve(f4s)); }
+    if (sky) { HJ_CUDA(c, w.q_sky.reserve((size_t)cap * 4)); HJ_CUDA(c, w.sk_d.reserve(f4s)); HJ_CUDA(c, w.sk_c.reserve(f4s)); }
     HJ_CUDA(c, w.counters.reserve(sizeof(WfCounters)));
     if (!w.stream) HJ_CUDA(c, cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
     if (!w.ev_acc) HJ_CUDA(c, cudaEventCreateWithFlags(&w.ev_acc, cudaEventDisableTiming));
@@ -530,6 +567,7 @@ static WfPtrs wf_ptrs(hj_ctx* c, WavefrontState& w) {
     P.sf0 = w.sf[0].as<float4>(); P.sf1 = w.sf[1].as<float4>(); P.sf2 = w.sf[2].as<float4>(); P.sf3 = w.sf[3].as<float4>();
     P.sh_o = w.sh_o.as<float4>(); P.sh_d = w.sh_d.as<float4>(); P.sh_c = w.sh_c.as<float4>();
     P.mi_o = w.mi_o.as<float4>(); P.mi_d = w.mi_d.as<float4>(); P.mi_a = w.mi_a.as<float4>(); P.mi_t = w.mi_t.as<float4>();
+    P.q_sky = w.q_sky.as<uint32_t>(); P.sk_d = w.sk_d.as<float4>(); P.sk_c = w.sk_c.as<float4>();
     P.cnt = w.counters.as<WfCounters>();
     P.aov_albedo = c->aov_albedo.as<float4>(); P.aov_normal = c->aov_normal.as<float4>();
     return P;
@@ -540,7 +578,7 @@ template <int INTEG>
 static int launch_shade_t(hj_ctx* c, uint32_t grid, cudaStream_t ps, const FrameK& F, const WfPtrs& P, int cur, int depth, uint32_t s0) {
     int n = 4;
     k_surface<INTEG><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
-    if (INTEG != HJ_INTEGRATOR_PT && c->S.n_lights >= 1) { k_nee<INTEG><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, s0); n++; }
+    if (INTEG != HJ_INTEGRATOR_PT && (c->S.n_lights >= 1 || (INTEG == HJ_INTEGRATOR_MIS && F.sky))) { k_nee<INTEG><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, s0); n++; }
     k_sample<INTEG, HJ_CLS_DISNEY><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
     k_sample<INTEG, HJ_CLS_GGX><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
     k_sample<INTEG, HJ_CLS_GLASS><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
@@ -598,7 +636,8 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     const uint32_t n_passes = n_spasses * bands;
     if ((uint32_t)np > n_passes) np = (int)std::max(1u, n_passes);
     const uint32_t cap = (uint32_t)((uint64_t)spass * band_pix);
-    for (int p = 0; p < np; p++) { int rc = wf_reserve(c, c->wf[p], cap, fp->integrator == HJ_INTEGRATOR_MIS, debug); if (rc) return rc; }
+    const bool sky = fp->sky_sampling != 0 && fp->integrator == HJ_INTEGRATOR_MIS;
+    for (int p = 0; p < np; p++) { int rc = wf_reserve(c, c->wf[p], cap, fp->integrator == HJ_INTEGRATOR_MIS, debug, sky); if (rc) return rc; }
     c->n_pipes_used = np;
     const size_t fb = (size_t)WH * sizeof(float4);
     HJ_CUDA(c, c->aov_color.reserve(fb)); HJ_CUDA(c, c->aov_albedo.reserve(fb)); HJ_CUDA(c, c->aov_normal.reserve(fb));
@@ -619,6 +658,7 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     F.cright = make_float3(fp->camera_right[0], fp->camera_right[1], fp->camera_right[2]);
     F.cf = fp->camera_f; F.ibl = fp->ibl_intensity;
     F.integrator = fp->integrator; F.max_depth = fp->max_depth; F.tonemap = fp->tonemap; F.jitter = fp->pixel_jitter; F.debug = debug;
+    F.sky = sky ? 1 : 0;
 
     int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
     const uint32_t grid = std::min(cdiv_u(cap, WF_THREADS), (uint32_t)sms * 16u);
@@ -676,6 +716,13 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
                 mark_end(ps);
                 launches++;
             }
+            if (sky) {                   // shadow rays of the sky samples (extension, after the light samples' so the additions keep that order)
+                mark_begin(0, ps);
+                if (count) k_trace<4, true><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
+                else k_trace<4, false><<<tgrid, HJ_TRACE_THREADS, 0, ps>>>(c->S, F, P, cur);
+                mark_end(ps);
+                launches++;
+            }
             if (fp->integrator == HJ_INTEGRATOR_MIS) {
                 mark_begin(0, ps);
                 // the debug records hash the MIS ray's closest hit whatever it is: they need the plain closest-hit query
@@ -727,7 +774,7 @@ int hj_wavefront_stats(hj_ctx* c) {
         HJ_CUDA(c, cudaMemcpy(&h, c->wf[p].counters.p, sizeof h, cudaMemcpyDeviceToHost));
         t.rays_extend += h.rays_extend; t.rays_shadow += h.rays_shadow; t.nodes += h.nodes; t.tris += h.tris;
         t.max_nodes = std::max(t.max_nodes, h.max_nodes); t.max_tris = std::max(t.max_tris, h.max_tris);
-        for (int m = 0; m < 3; m++) for (int k = 0; k < 8; k++) t.diag[m][k] += h.diag[m][k];
+        for (int m = 0; m < 4; m++) for (int k = 0; k < 8; k++) t.diag[m][k] += h.diag[m][k];
     }
     if (c->opt_count_fetches && getenv("HJ_TRACE_DIAG"))
         for (int m = 0; m < 3; m++) {

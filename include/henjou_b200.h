@@ -134,7 +134,11 @@ typedef struct hj_frame_params {
     int32_t tonemap;              /* hj_tonemap */
     int32_t pixel_jitter;         /* 1 = first CMJ draw of each sample jitters the pixel */
     int32_t debug_paths;          /* 1 = record HJ_AOV_PATH_* (needs n_samples*W*H*24 bytes) */
-    int32_t reserved;
+    int32_t sky_sampling;         /* 0 (default): the reference's behaviour — the sky is reached by BSDF sampling only (rt.h:417-419).
+                                     1 (MIS integrator only): EXTENSION, SURVEY §8 f4 — at every non-specular vertex one direction is also drawn
+                                     from the sky image's luminance x sin(theta) table (built on the GPU at hj_scene_upload), one more shadow ray,
+                                     balance heuristic between the two; one extra RNG dimension per vertex. Restated in oracle/libhjo.so; the
+                                     reference-headers build refuses it. */
 } hj_frame_params;
 
 typedef struct hj_stats {

@@ -100,6 +100,7 @@ struct Scene {
     std::vector<hj_material> materials;
     std::vector<Image8> textures;
     ImageF ibl;
+    std::vector<float> sky_row_cdf, sky_marg;   // sky_sampling extension: running sums of luminance x sin(theta_row) per row / of the row totals
     Image8 lut;
     bool has_lut = false;
     // per-frame state (≙ updateIASMatrix, renderer.h:257-291)
@@ -139,6 +140,22 @@ static inline bool load_scene(Scene& S, const hj_scene_desc* d) {
         S.ibl.w = d->ibl_width; S.ibl.h = d->ibl_height;
         const float4* p = (const float4*)d->ibl_rgba32f; S.ibl.px.assign(p, p + (size_t)S.ibl.w * S.ibl.h);
     } else { S.ibl.w = S.ibl.h = 1; S.ibl.px.assign(1, float4{0, 0, 0, 0}); }
+    {   // the table of the sky_sampling extension: the loops of k_sky_rows / k_sky_marginal (csrc/hj_api.cu), same float addition order
+        const int W = S.ibl.w, H = S.ibl.h;
+        S.sky_row_cdf.assign((size_t)W * H, 0.0f); S.sky_marg.assign((size_t)H, 0.0f);
+        for (int y = 0; y < H; y++) {
+            const float st = hjo_sinf(M_PIf * ((float)y + 0.5f) / (float)H);
+            float run = 0.0f;
+            for (int x = 0; x < W; x++) {
+                const float4 c = S.ibl.px[(size_t)y * W + x];
+                const float lum = 0.2126f * c.x + 0.7152f * c.y + 0.0722f * c.z;
+                run += fmaxf(lum, 0.0f) * st;
+                S.sky_row_cdf[(size_t)y * W + x] = run;
+            }
+        }
+        float run = 0.0f;
+        for (int y = 0; y < H; y++) { run += S.sky_row_cdf[(size_t)y * W + W - 1]; S.sky_marg[y] = run; }
+    }
     S.has_lut = d->lut_rgba8 && d->lut_width > 0;
     if (S.has_lut) {
         S.lut.w = d->lut_width; S.lut.h = d->lut_height; S.lut.srgb = 0;
@@ -338,6 +355,53 @@ static inline float3 sky_radiance(const Scene& S, const float3& dir, float ibl_i
     float theta = hjo_acosf(clamp(dir.y, -1.0f, 1.0f));
     float4 c = bilinearF(S.ibl, phi * (1.0f / (2.0f * M_PIf)), theta * (1.0f / M_PIf));
     return ibl_intensity * make_float3(c);
+}
+
+// ---- sky importance sampling (extension behind hj_frame_params::sky_sampling; the reference BSDF-samples the sky only, rt.h:417-419).
+// Restated operation for operation from csrc/hj_scene.cuh (sky_pdf_texel / sky_search / sky_sample / sky_pdf).
+static inline float sky_texel_weight(const Scene& S, int x, int y) {
+    const float* row = S.sky_row_cdf.data() + (size_t)y * S.ibl.w;
+    return row[x] - (x ? row[x - 1] : 0.0f);
+}
+static inline float sky_pdf_texel(const Scene& S, int x, int y, float sin_theta) {
+    const float total = S.sky_marg[S.ibl.h - 1];
+    if (!(total > 0.0f) || !(sin_theta > 0.0f)) return 0.0f;
+    const float pdf_uv = sky_texel_weight(S, x, y) * (float)S.ibl.w * (float)S.ibl.h / total;
+    return pdf_uv / (2.0f * M_PIf * M_PIf * sin_theta);
+}
+static inline int sky_search(const float* cdf, int n, float t) {
+    int lo = 0, hi = n - 1;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (cdf[mid] > t) hi = mid; else lo = mid + 1; }
+    return lo;
+}
+static inline float3 sky_sample(const Scene& S, const float2& xi, float& pdf) {
+    pdf = 0.0f;
+    const int W = S.ibl.w, H = S.ibl.h;
+    const float total = S.sky_marg[H - 1];
+    if (!(total > 0.0f)) return make_float3(0.0f, 1.0f, 0.0f);
+    const float ty = xi.x * total;
+    const int y = sky_search(S.sky_marg.data(), H, ty);
+    const float* row = S.sky_row_cdf.data() + (size_t)y * W;
+    const float tx = xi.y * row[W - 1];
+    const int x = sky_search(row, W, tx);
+    const float px = x ? row[x - 1] : 0.0f, fx = row[x] - px;
+    const float py = y ? S.sky_marg[y - 1] : 0.0f, fy = S.sky_marg[y] - py;
+    const float du = fx > 0.0f ? clamp((tx - px) / fx, 0.0f, 0.99999994f) : 0.5f;
+    const float dv = fy > 0.0f ? clamp((ty - py) / fy, 0.0f, 0.99999994f) : 0.5f;
+    const float u = ((float)x + du) / (float)W, v = ((float)y + dv) / (float)H;
+    const float pa = 2.0f * M_PIf * u, ta = M_PIf * v;
+    const float sp = hjo_sinf(pa), cp = hjo_cosf(pa), st = hjo_sinf(ta), ct = hjo_cosf(ta);
+    pdf = sky_pdf_texel(S, x, y, st);
+    return make_float3(st * cp, ct, st * sp);
+}
+static inline float sky_pdf(const Scene& S, const float3& dir) {
+    float phi = hjo_atan2f(dir.z, dir.x);
+    if (phi < 0.0f) phi += 2.0f * M_PIf;
+    const float theta = hjo_acosf(clamp(dir.y, -1.0f, 1.0f));
+    const float u = phi * (1.0f / (2.0f * M_PIf)), v = theta * (1.0f / M_PIf);
+    int x = (int)(u * (float)S.ibl.w), y = (int)(v * (float)S.ibl.h);
+    x = x < 0 ? 0 : (x > S.ibl.w - 1 ? S.ibl.w - 1 : x); y = y < 0 ? 0 : (y > S.ibl.h - 1 ? S.ibl.h - 1 : y);
+    return sky_pdf_texel(S, x, y, hjo_sinf(theta));
 }
 
 // D4/D5: what __closesthit__ch leaves in the payload; miss -> D6.

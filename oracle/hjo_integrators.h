@@ -169,6 +169,24 @@ static inline float3 integrate_mis(const float3& o0, const float3& d0, Sampler& 
                 if (!trace_shadow(prd.position, ld, 0.001f, dist - 0.001f)) L += contrib;
             } else g_trace.rays_shadow++;   // the reference traces it; its result cannot change L
         }
+        if (g_trace.sky_sampling) {   // EXTENSION (hj_frame_params::sky_sampling): a direction drawn from the sky's luminance table, MIS against the BSDF pdf
+            const float2 xi = draw2(st);
+            float spdf;
+            const float3 sd = sky_sample(*g_trace.scene, xi, spdf);
+            bool useful = false; float3 contrib = make_float3(0.0f);
+            if (spdf > 0.0f && !prd.is_specular) {
+                const float c1 = absdot(n, sd);
+                const float3 lwi = to_local(sd, t, n, b);
+                const float3 f = bsdf.eval(lwo, lwi);
+                const float w = spdf / (spdf + bsdf.pdf(lwo, lwi));
+                contrib = thr * (f * c1 / spdf) * w * sky_radiance(*g_trace.scene, sd, g_trace.ibl_intensity);
+                useful = !is_zero(contrib);
+            }
+            if (useful) {
+                g_trace.traced_shadow++;
+                if (!trace_shadow(prd.position, sd, 0.001f, 1e16f)) L += contrib;
+            }
+        }
         {   // BSDF sampling towards emitters, rt.h:383-420
             float ppdf = 1.0f;                  // defined (reference: uninitialised)
             float3 lwi = {0.0f, 1.0f, 0.0f};    // defined (reference: uninitialised)
@@ -189,6 +207,9 @@ static inline float3 integrate_mis(const float3& o0, const float3& d0, Sampler& 
                     float w = ppdf / (ppdf + lpdf);
                     L += thr * w * c1 * lh.emission * f / ppdf;
                 }
+            } else if (g_trace.sky_sampling && !prd.is_specular) {      // extension: balance heuristic against the sky's light-sampling pdf
+                const float w = ppdf / (ppdf + sky_pdf(*g_trace.scene, wi));
+                L += thr * w * f * c1 * lh.emission / ppdf;
             } else {
                 L += thr * f * c1 * lh.emission / ppdf;
             }

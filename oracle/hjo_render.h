@@ -49,6 +49,7 @@ static int render_rows(Context& C, const hj_frame_params& fp, int n_threads, uin
         g_trace = TraceCtx();
         g_trace.scene = &C.scene;
         g_trace.ibl_intensity = fp.ibl_intensity;
+        g_trace.sky_sampling = fp.sky_sampling != 0 && fp.integrator == HJ_INTEGRATOR_MIS;
         g_shade.scene = &C.scene;
 #pragma omp for schedule(dynamic, 1)
         for (uint32_t y = y0; y < y1; y++) {
@@ -108,6 +109,7 @@ static int path_events(Context& C, const hj_frame_params& fp, uint32_t pix, uint
     const float3 cup = make_float3(fp.camera_up[0], fp.camera_up[1], fp.camera_up[2]);
     const float3 cright = make_float3(fp.camera_right[0], fp.camera_right[1], fp.camera_right[2]);
     g_trace = TraceCtx(); g_trace.scene = &C.scene; g_trace.ibl_intensity = fp.ibl_intensity; g_shade.scene = &C.scene;
+    g_trace.sky_sampling = fp.sky_sampling != 0 && fp.integrator == HJ_INTEGRATOR_MIS;
     const uint32_t x = pix % W, y = pix / W;
     typename Policy::State st = Policy::make((uint64_t)s, fp.frame, pix);
     float jx = 0.0f, jy = 0.0f;

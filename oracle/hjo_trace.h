@@ -24,6 +24,7 @@ static inline float3 lut_lookup(float u, float v) {
 struct TraceCtx {
     const Scene* scene = nullptr;
     float ibl_intensity = 1.0f;
+    bool sky_sampling = false;      // hj_frame_params::sky_sampling with the MIS integrator (extension)
     PathDebug dbg;
     uint64_t rays_extend = 0, rays_shadow = 0;       // every RayTrace / TraceOcculution of the reference
     uint64_t traced_extend = 0, traced_shadow = 0;   // rays the wavefront build actually traces (zero-weight rays skipped)

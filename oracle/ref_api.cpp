@@ -92,7 +92,7 @@ int hjo_accel_build(hjo_ctx* c, const float* xf, const float* ixf, uint32_t n, i
 }
 int hjo_render(hjo_ctx* c, const hj_frame_params* fp, int n_threads, uint32_t y0, uint32_t y1, hjo_render_out* out) {
     if (!c || !fp || !out) return HJ_ERR_INVALID;
-    if (fp->max_depth != 10) return HJ_ERR_INVALID;
+    if (fp->max_depth != 10 || fp->sky_sampling) return HJ_ERR_INVALID;    // the reference's integrators: depth 10, no sky sampling
     bind_params(c->c.scene);
     params.image_width = fp->width; params.image_height = fp->height; params.spp = fp->spp; params.frame = fp->frame;
     params.ibl_intensity = fp->ibl_intensity;

@@ -12,17 +12,17 @@ import bench
 import henjou_renderer_b200 as hj
 from henjou_renderer_b200 import abi
 
-args = [a for a in sys.argv[1:] if not a.startswith("--")]
-flags = [a for a in sys.argv[1:] if a.startswith("--")]
+argv = sys.argv[1:]
+stats_json = None
+if "--stats-json" in argv:
+    k = argv.index("--stats-json")
+    stats_json = argv[k + 1]
+    del argv[k:k + 2]
+flags = [a for a in argv if a.startswith("--")]
+args = [a for a in argv if not a.startswith("--")]
 workload = args[0] if args else "c2"
 spp = int(args[1]) if len(args) > 1 else 4
 opts = dict(a.split("=") for a in args[2:])
-stats_json = None
-if "--stats-json" in sys.argv:
-    stats_json = sys.argv[sys.argv.index("--stats-json") + 1]
-    opts.pop(stats_json, None)
-    args = [a for a in args if a != stats_json]
-    opts = dict(a.split("=") for a in args[2:])
 scene, cfg, desc = bench.make_workload(workload)
 cfg["spp"] = spp
 r = hj.Renderer(0)
