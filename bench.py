@@ -59,7 +59,7 @@ def make_workload(name):
     if name == "c5":
         s = scenes.icosphere_field()
         return s, dict(width=3840, height=2160, spp=8, max_depth=10, integrator=abi.INTEGRATOR_MIS, frame=1), \
-            "C5 ~10M-triangle icosphere field 3840x2160, 8 spp per step, MIS, depth 10"
+            "C5 ~10M-triangle icosphere field 3840x2160, 8 spp, MIS, depth 10"
     raise SystemExit("unknown workload " + name)
 
 
@@ -161,6 +161,8 @@ def gpu_arm(args, rank, world, local_rank):
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     scene, cfg, desc = make_workload(args.workload)
+    if args.spp > 0:
+        desc = desc.replace("%d spp" % cfg["spp"], "%d spp" % args.spp); cfg["spp"] = args.spp
     W, H, spp = cfg["width"], cfg["height"], cfg["spp"]
     r = hj.Renderer(local_rank)
     r.upload(scene)
@@ -254,7 +256,11 @@ def gpu_arm(args, rank, world, local_rank):
     barrier()
     e_rays, t0 = 0, time.perf_counter()
     for _ in range(args.steps):
-        r.upload(scene); r.build_accel(xf, inv); r.render(fp, sync=False)
+        if world > 1:
+            r.comm_upload(scene, 0)          # hj_comm_scene_upload: one PCIe copy of the geometry on rank 0, ncclBroadcast over NVLink to the others
+        else:
+            r.upload(scene)
+        r.build_accel(xf, inv); r.render(fp, sync=False)
         if world > 1:
             r.comm_reduce()
         r.sync()
@@ -268,12 +274,14 @@ def gpu_arm(args, rank, world, local_rank):
         tmax = tt.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = tt.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         e_t, e_rays = float(tmax[0]), int(tsum[1])
-    out["e2e"] = dict(value=round(e_rays / e_t / 1e6, 2), unit="Mrays/s", h2d_bytes_per_step=int(h2d) * world, d2h_bytes_per_step=int(d2h) * world,
+    small = scene.prim_offsets.nbytes + xf.nbytes + inv.nbytes + (scene.lut.nbytes if scene.lut is not None else 0) + scene.ibl.nbytes
+    out["e2e"] = dict(value=round(e_rays / e_t / 1e6, 2), unit="Mrays/s", h2d_bytes_per_step=int(h2d) + int(small) * (world - 1), d2h_bytes_per_step=int(d2h) * world,
+                      nvlink_broadcast_bytes_per_step=int(h2d - small) * (world - 1) if world > 1 else 0,
                       ms_per_step=round(1e3 * e_t / args.steps, 3), checksum=float(np.nanmean(np.where(np.isfinite(color[..., :3]), color[..., :3], np.nan))),
                       non_finite_pixels=int((~np.isfinite(color[..., :3]).all(-1)).sum()),
                       host_memory="pageable" if args.pageable else "pinned (hj_host_pin)")
     r.unpin(*pinned)
-    if rank == 0 and world == 1:
+    if rank == 0 and world == 1 and not args.no_roofline:
         # ---- roofline of the traversal kernels: bytes from a counters pass, time from an event-pair pass
         r.set_option("count_fetches", 1); r.render(fp); sc = r.stats(); r.set_option("count_fetches", 0)
         r.set_option("time_stages", 1); r.render(fp); stt = r.stats(); r.set_option("time_stages", 0)
@@ -339,6 +347,8 @@ def reference_arm(args, rank, world):
     if rank != 0:
         return
     scene, cfg, desc = make_workload(args.workload)
+    if args.spp > 0:
+        desc = desc.replace("%d spp" % cfg["spp"], "%d spp" % args.spp); cfg["spp"] = args.spp
     vals, info = cpu_arm(scene, cfg, budget_s=args.cpu_budget, steps=args.steps, warmup=min(args.warmup, 1))
     v = float(np.mean(vals))
     out = dict(metric="Mrays/s", value=round(v, 3), unit="Mrays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
@@ -362,6 +372,8 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--pageable", action="store_true", help="e2e leg with pageable host buffers (no hj_host_pin)")
+    ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (C5 as BASELINE.json states it: --workload c5 --spp 1024)")
+    ap.add_argument("--no-roofline", action="store_true", help="skip the counters / stage-timing passes and the CPU baseline (long workloads)")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="N > 1: split the fixed frame (strong, default) or 64 spp per rank (weak)")
     ap.add_argument("--as-rank-of", type=int, default=1, help="one GPU: render rank 0's slice of an N-way strong split (predicts the split without the box)")
     args = ap.parse_args()

@@ -158,9 +158,15 @@ int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
 
 static float srgb_to_linear(float v) { return (v <= 0.04045f) ? v / 12.92f : hjm_powf((v + 0.055f) / 1.055f, 2.4f); }   // hj_libm.h: same table as the oracle's
 
-int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
+int hj_scene_upload_impl(hj_ctx* c, const hj_scene_desc* d, bool geometry_from_host);
+
+int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) { return hj_scene_upload_impl(c, d, true); }
+
+// geometry_from_host = false (hj_comm_scene_upload on a rank that is not the root): the five big SceneData arrays are only
+// allocated; their contents arrive over NVLink. Everything small (offsets, materials, textures, lights, sky, LUT) is uploaded as usual.
+int hj_scene_upload_impl(hj_ctx* c, const hj_scene_desc* d, bool geometry_from_host) {
     if (!c) return HJ_ERR_INVALID;
-    HJ_REQUIRE(c, d && d->vertices && d->indices && d->material_ids && d->prim_offsets, HJ_ERR_INVALID, "hj_scene_upload: missing geometry arrays");
+    HJ_REQUIRE(c, d && d->prim_offsets && (!geometry_from_host || (d->vertices && d->indices && d->material_ids)), HJ_ERR_INVALID, "hj_scene_upload: missing geometry arrays");
     HJ_REQUIRE(c, d->n_instances > 0 && d->n_triangles > 0 && d->n_vertices > 0, HJ_ERR_INVALID, "hj_scene_upload: empty scene");
     HJ_REQUIRE(c, d->n_materials > 0 && d->materials, HJ_ERR_INVALID, "hj_scene_upload: no materials");
     HJ_REQUIRE(c, d->prim_offsets[0] == 0, HJ_ERR_INVALID, "hj_scene_upload: prim_offsets[0] must be 0");
@@ -175,25 +181,30 @@ int hj_scene_upload(hj_ctx* c, const hj_scene_desc* d) {
     c->bvh.have_topology = false;
     int rc;
     const size_t nv = d->n_vertices, nt = d->n_triangles;
-    if ((rc = upload(c, c->d_vertices, d->vertices, 3 * nv))) return rc;
-    {   // normals default to +y and uvs to 0 when absent (the loader always provides them, gltfloader.h:1460-1482)
-        std::vector<float> tmp;
-        if (!d->normals) { tmp.assign(3 * nv, 0.0f); for (size_t i = 0; i < nv; i++) tmp[3 * i + 1] = 1.0f; }
-        if ((rc = upload(c, c->d_normals, d->normals ? d->normals : tmp.data(), 3 * nv))) return rc;
-        if (!d->normals) HJ_CUDA(c, cudaStreamSynchronize(c->stream));          // tmp is reused / freed below
-        if (!d->texcoords) tmp.assign(2 * nv, 0.0f);
-        if ((rc = upload(c, c->d_texcoords, d->texcoords ? d->texcoords : tmp.data(), 2 * nv))) return rc;
-        if (!d->texcoords) HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (geometry_from_host) {
+        if ((rc = upload(c, c->d_vertices, d->vertices, 3 * nv))) return rc;
+        {   // normals default to +y and uvs to 0 when absent (the loader always provides them, gltfloader.h:1460-1482)
+            std::vector<float> tmp;
+            if (!d->normals) { tmp.assign(3 * nv, 0.0f); for (size_t i = 0; i < nv; i++) tmp[3 * i + 1] = 1.0f; }
+            if ((rc = upload(c, c->d_normals, d->normals ? d->normals : tmp.data(), 3 * nv))) return rc;
+            if (!d->normals) HJ_CUDA(c, cudaStreamSynchronize(c->stream));          // tmp is reused / freed below
+            if (!d->texcoords) tmp.assign(2 * nv, 0.0f);
+            if ((rc = upload(c, c->d_texcoords, d->texcoords ? d->texcoords : tmp.data(), 2 * nv))) return rc;
+            if (!d->texcoords) HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+        }
+        if ((rc = upload(c, c->d_indices, d->indices, 3 * nt))) return rc;
+        if ((rc = upload(c, c->d_material_ids, d->material_ids, nt))) return rc;
+    } else {
+        HJ_CUDA(c, c->d_vertices.reserve(3 * nv * 4)); HJ_CUDA(c, c->d_normals.reserve(3 * nv * 4)); HJ_CUDA(c, c->d_texcoords.reserve(2 * nv * 4));
+        HJ_CUDA(c, c->d_indices.reserve(3 * nt * 4)); HJ_CUDA(c, c->d_material_ids.reserve(nt * 4));
     }
-    if ((rc = upload(c, c->d_indices, d->indices, 3 * nt))) return rc;
-    if ((rc = upload(c, c->d_material_ids, d->material_ids, nt))) return rc;
     if ((rc = upload(c, c->d_prim_offsets, d->prim_offsets, (size_t)d->n_instances))) return rc;
     // owning instance per triangle: derived on the device from prim_offsets (no host pass, no extra upload)
     HJ_CUDA(c, c->d_tri_inst.reserve(nt * sizeof(uint32_t)));
     k_tri_inst<<<(uint32_t)((nt + 255) / 256), 256, 0, c->stream>>>(c->d_prim_offsets.as<uint32_t>(), d->n_instances, d->n_triangles, c->d_tri_inst.as<uint32_t>());
     // range checks of the two big index arrays run on the host while the copies above are in flight (they come out of
     // page-locked memory when the caller used hj_host_pin); a violation leaves the context without a scene
-    {
+    if (geometry_from_host) {
         uint32_t max_index = 0, max_material = 0;
         const uint32_t* idx = d->indices; const size_t ni = 3 * nt;
         for (size_t i = 0; i < ni; i++) max_index = idx[i] > max_index ? idx[i] : max_index;

@@ -283,26 +283,36 @@ HJ_DI float3 sample_class(const DevScene& S, const Surface& prd, const float3& l
     return dz.sample(S, lwo, lwi, pdf, st);
 }
 
+// PAIRED (MIS integrator, Disney and glass classes — a fixed number of draws per sample): the two samples of a surface run on
+// two ADJACENT LANES instead of one after the other on one thread (lane 2j: the MIS sample, lane 2j+1: the continuation sample
+// and the roulette). Same arithmetic, same RNG dimensions; but a warp now fetches every instruction of the 50 KB sampling
+// code once for 16 surfaces x 2 samples instead of twice for 32 x 1 — instruction-cache misses were this kernel's top stall
+// (r01-w ncu: no_instruction 3.3 cycles per issue at 0.46 IPC). The EC-GGX class draws 2k+1 dimensions per sample (k = scattering
+// orders taken), so its second sample cannot start before the first has finished: it keeps the 2-trip loop.
 template <int INTEG, int CLS>
 __global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
-    const uint32_t n = P.cnt->n_cls[CLS];
+    constexpr bool PAIRED = INTEG == HJ_INTEGRATOR_MIS && CLS != HJ_CLS_GGX;
+    constexpr uint32_t DRAWS = CLS == HJ_CLS_GLASS ? 1u : 2u;               // RNG calls of one sample of a paired class
+    const uint32_t n = P.cnt->n_cls[CLS] * (PAIRED ? 2u : 1u);
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
-        const uint32_t slot = (i < n) ? P.q_cls[CLS][i] : 0xffffffffu;
+        const uint32_t slot = (i < n) ? P.q_cls[CLS][PAIRED ? (i >> 1) : i] : 0xffffffffu;
+        const int k_first = PAIRED ? (int)(i & 1u) : (INTEG == HJ_INTEGRATOR_MIS ? 0 : 1), k_last = PAIRED ? k_first : 1;
         bool push_mis = false, push_next = false;
+        Surface prd; float3 d = f3(0.0f), thr = f3(0.0f); uint32_t rng0 = 0;
+        if (slot != 0xffffffffu) { prd = load_surface(P, slot); d = f3(P.ray_d[slot]); thr = f3(P.thr[slot]); rng0 = P.rng[slot]; }
+        if (PAIRED) __syncwarp();      // a lane pair shares its slot: both lanes have read the slot's state before the second one rewrites it
         if (slot != 0xffffffffu) {
-            const Surface prd = load_surface(P, slot);
-            const float3 d = f3(P.ray_d[slot]);
-            float3 thr = f3(P.thr[slot]);
-            Sampler st; st.n_spp = s0 + slot / F.npix; st.scramble = F.frame; st.image_idx = F.pix0 + slot % F.npix; st.depth = P.rng[slot];
+            Sampler st; st.n_spp = s0 + slot / F.npix; st.scramble = F.frame; st.image_idx = F.pix0 + slot % F.npix; st.depth = rng0;
             if (INTEG != HJ_INTEGRATOR_PT && S.n_lights >= 1) st.depth += 2;     // light pick + barycentrics (light_sample.h:18,60)
             if (INTEG == HJ_INTEGRATOR_MIS && F.sky) st.depth += 1;               // the sky sample's draw (k_nee)
+            if (PAIRED && k_first == 1) st.depth += DRAWS + 1u;                   // the MIS sample's draws and the dead draw (rt.h:426) run on the lane before
             float3 t, b; const float3 nrm = prd.normal;
             onb(nrm, t, b);
             const float3 lwo = to_local(-d, t, nrm, b);
             if (INTEG == HJ_INTEGRATOR_NEE) draw_skip(st);                      // dead draw, rt.h:266
 #pragma unroll 1
-            for (int k = (INTEG == HJ_INTEGRATOR_MIS ? 0 : 1); k < 2; k++) {
+            for (int k = k_first; k <= k_last; k++) {
                 float pdf = 1.0f;                   // defined (reference: uninitialised in MIS)
                 float3 lwi = f3(0.0f, 1.0f, 0.0f);  // defined (reference: uninitialised in MIS)
                 const float3 f = sample_class<CLS>(S, prd, lwo, lwi, pdf, st);

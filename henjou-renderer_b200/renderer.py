@@ -55,6 +55,7 @@ def load_library():
     L.hj_comm_unique_id.argtypes = [vp]
     L.hj_comm_init.argtypes = [vp, vp, C.c_int, C.c_int]
     L.hj_comm_reduce.argtypes = [vp]
+    L.hj_comm_scene_upload.argtypes = [vp, C.POINTER(abi.hj_scene_desc), C.c_int]
     _lib = L
     return L
 
@@ -179,6 +180,12 @@ class Renderer:
     def comm_init(self, unique_id, rank, nranks):
         buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
         self._check(self.L.hj_comm_init(self.ctx, buf, rank, nranks), "hj_comm_init")
+
+    def comm_upload(self, scene, root=0):
+        """hj_comm_scene_upload: the geometry crosses PCIe on `root` only and is broadcast to the other ranks over NVLink."""
+        self.scene = scene
+        desc = scene.to_desc()
+        self._check(self.L.hj_comm_scene_upload(self.ctx, C.byref(desc), int(root)), "hj_comm_scene_upload")
 
     def comm_reduce(self):
         self._check(self.L.hj_comm_reduce(self.ctx), "hj_comm_reduce")

@@ -250,6 +250,11 @@ int hj_libm_eval(hj_ctx* ctx, int fn, const float* a, const float* b, float* out
  * float4 accumulation buffer per frame over NCCL/NVLink. unique_id is the 128-byte ncclUniqueId. */
 int hj_comm_unique_id(void* unique_id_128);
 int hj_comm_init(hj_ctx* ctx, const void* unique_id_128, int rank, int nranks);
+/* hj_scene_upload for the replicated scene of a multi-GPU job, called by every rank of the communicator with the same counts: the five
+ * big SceneData arrays (vertices, normals, texcoords, indices, material_ids) cross PCIe ONCE, on `root`, and reach the other ranks by
+ * ncclBroadcast over NVLink / NVSwitch; on the other ranks those five pointers are not read (they may be NULL). The small arrays
+ * (prim_offsets, materials, textures, lights, sky, LUT) are read from every rank's own description. */
+int hj_comm_scene_upload(hj_ctx* ctx, const hj_scene_desc* scene, int root);
 /* all-reduces HJ_AOV_ACCUM over the communicator and finalises the colour/RGBA8 AOVs on every rank. */
 int hj_comm_reduce(hj_ctx* ctx);
 

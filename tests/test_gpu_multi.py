@@ -47,6 +47,13 @@ def _worker(rank, world, tmp, spp):
         r.render(hj.frame_params(scene, 96, 64, spp, frame=1, max_depth=8, tonemap=abi.TONEMAP_ACES))
         full = [r.readback(a).copy() for a in (abi.AOV_ACCUM, abi.AOV_COLOR, abi.AOV_RGBA8)]
     r.comm_init(uid, rank, world)
+    # hj_comm_scene_upload: the geometry crosses PCIe on rank 0 only; rank 1 offers poisoned arrays that must never be read
+    import copy
+    shared = copy.copy(scene)
+    if rank != 0:
+        shared.vertices = np.full_like(scene.vertices, np.nan); shared.normals = np.full_like(scene.normals, np.nan)
+        shared.texcoords = np.full_like(scene.texcoords, np.nan); shared.indices = np.zeros_like(scene.indices); shared.material_ids = np.zeros_like(scene.material_ids)
+    r.comm_upload(shared, 0); r.build_accel(xf, inv)
     b, e = hj.sample_slice(spp, rank, world)
     r.render(hj.frame_params(scene, 96, 64, spp, frame=1, max_depth=8, tonemap=abi.TONEMAP_ACES, sample_begin=b, sample_end=e), sync=False)
     r.comm_reduce()

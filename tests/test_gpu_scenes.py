@@ -280,7 +280,11 @@ def test_sky_importance_sampling_extension(gpu):
         gpu.render(hj.frame_params(s, 64, 64, spp, frame=frame, max_depth=6, integrator=abi.INTEGRATOR_MIS, sky_sampling=on))
         return gpu.readback(abi.AOV_COLOR)[..., :3].astype(np.float64)
     ref_on, ref_off = img(16384, 1, 1), img(16384, 0, 2)
-    rel = lambda a, b: float(np.mean(((a - b) ** 2).sum(-1) / ((ref_on ** 2).sum(-1) + 1e-2)))
+    # about one path in 1e8 ends in NaN (a 0/0 inside the reference's BSDF code, reproduced on purpose): leave such pixels out
+    ok = np.isfinite(ref_on).all(-1) & np.isfinite(ref_off).all(-1)
+    assert ok.mean() > 0.999
+    ref_on, ref_off = np.where(ok[..., None], ref_on, 0.0), np.where(ok[..., None], ref_off, 0.0)
+    rel = lambda a, b: float(np.mean((((np.where(ok[..., None], a, 0.0) - b) ** 2).sum(-1) / ((ref_on ** 2).sum(-1) + 1e-2))[ok]))
     assert abs(ref_on.mean() - ref_off.mean()) <= 5e-3 * ref_on.mean(), (ref_on.mean(), ref_off.mean())
     assert rel(ref_off, ref_on) < 5e-3
     e_on, e_off = rel(img(16, 1, 3), ref_on), rel(img(16, 0, 3), ref_on)

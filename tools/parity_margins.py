@@ -38,12 +38,14 @@ def cases(size, spp):
     cam = dict(position=np.array([4.5, 0.2, 0.1], np.float32), direction=np.array([-1, 0, 0], np.float32), fov=0.48)
     c2 = scenes.rtcamp_like(statue_subdiv=4, detail=0.08)
     c3 = scenes.metaglass_room(subdiv=3)
+    c5 = scenes.icosphere_field(n_spheres=300, subdiv=3)
     h = size * 9 // 16
     for name, integ in (("PT", abi.INTEGRATOR_PT), ("NEE", abi.INTEGRATOR_NEE), ("MIS", abi.INTEGRATOR_MIS)):
         yield "C1 cornelbox %s depth 10" % name, c, dict(width=size, height=size, spp=spp, frame=1, max_depth=10, integrator=integ), 1 / 24
     yield "cornelbox_texture_test MIS depth 10", ct, dict(width=size, height=size, spp=spp, frame=0, max_depth=10, camera=cam), 0.0
     yield "C2 stand-in (thin-film, EC-GGX, clearcoat) MIS depth 10", c2, dict(width=size, height=h, spp=spp, frame=1, max_depth=10), 1 / 24
     yield "C3 stand-in (ior-1.5 metaglass) MIS depth 10", c3, dict(width=size, height=h, spp=spp, frame=3, max_depth=10), 0.0
+    yield "C5 stand-in (390 k-triangle icosphere field) MIS depth 10", c5, dict(width=size, height=h, spp=max(1, spp // 2), frame=1, max_depth=10), 0.0
     yield "C3 stand-in (ior-1.5 metaglass) MIS depth 32", c3, dict(width=size, height=h, spp=max(1, spp // 2), frame=3, max_depth=32), 0.0
 
 
