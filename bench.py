@@ -165,6 +165,9 @@ def gpu_arm(args, rank, world, local_rank):
         desc = desc.replace("%d spp" % cfg["spp"], "%d spp" % args.spp); cfg["spp"] = args.spp
     W, H, spp = cfg["width"], cfg["height"], cfg["spp"]
     r = hj.Renderer(local_rank)
+    for kv in args.opt:                                # kernel-layout options for A/B runs (none changes a result)
+        k, v = kv.split("=")
+        r.set_option(k, int(v))
     r.upload(scene)
     xf, inv = scene.transforms(cfg["frame"] / 24.0)
     r.build_accel(xf, inv)
@@ -372,6 +375,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--pageable", action="store_true", help="e2e leg with pageable host buffers (no hj_host_pin)")
+    ap.add_argument("--opt", action="append", default=[], help="hj_set_option key=value (repeatable), for A/B runs")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (C5 as BASELINE.json states it: --workload c5 --spp 1024)")
     ap.add_argument("--no-roofline", action="store_true", help="skip the counters / stage-timing passes and the CPU baseline (long workloads)")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="N > 1: split the fixed frame (strong, default) or 64 spp per rank (weak)")

@@ -115,6 +115,7 @@ void hj_destroy(hj_ctx* c) {
                       &c->aov_color, &c->aov_albedo, &c->aov_normal, &c->aov_rgba8, &c->aov_accum, &c->aov_path_rad, &c->aov_path_ids,
                       &c->aov_output, &c->aov_output_rgba8, &c->post_tmp[0], &c->post_tmp[1]};
     for (DevBuf* b : bufs) b->release();
+    for (DevBuf& b : c->trace_scratch) b.release();
     hj_bvh_release(c);
     for (WavefrontState& w : c->wf) {
         for (DevBuf* b : w.all) if (b) b->release();
@@ -143,6 +144,7 @@ int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
     else if (!strcmp(key, "bands")) { HJ_REQUIRE(c, value >= 0 && value <= 64, HJ_ERR_INVALID, "hj_set_option: bands must be 0 (auto) .. 64"); c->opt_bands = (int)value; }
     else if (!strcmp(key, "ploc_tail")) { c->opt_ploc_tail = value != 0; c->bvh.have_topology = false; }
     else if (!strcmp(key, "verify_accel")) c->opt_verify_accel = value != 0;
+    else if (!strcmp(key, "nan_repair")) c->opt_nan_repair = value != 0;
     else if (!strcmp(key, "mis_emitter_first")) c->opt_mis_emitter_first = value != 0;
     else if (!strcmp(key, "denoise_iterations")) { HJ_REQUIRE(c, value >= 0 && value <= 8, HJ_ERR_INVALID, "hj_set_option: denoise_iterations must be 0..8"); c->opt_denoise_iterations = (int)value; }
     else if (!strncmp(key, "denoise_sigma_", 14)) {

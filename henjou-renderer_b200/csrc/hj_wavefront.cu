@@ -32,6 +32,7 @@ struct FrameK {
     uint32_t pix0, npix;      // this pass covers pixels [pix0, pix0 + npix) of its samples: slot = s_local * npix + (pixel - pix0)
     float3 cpos, cdir, cup, cright; float cf, ibl;
     int integrator, max_depth, tonemap, jitter, debug;
+    int nan_repair;           // option nan_repair: non-finite samples are left out of the pixel's sum and of its sample count
     int sky;                  // hj_frame_params::sky_sampling (MIS only): light-sampled sky with MIS, an extension over the reference
 };
 
@@ -283,36 +284,30 @@ HJ_DI float3 sample_class(const DevScene& S, const Surface& prd, const float3& l
     return dz.sample(S, lwo, lwi, pdf, st);
 }
 
-// PAIRED (MIS integrator, Disney and glass classes — a fixed number of draws per sample): the two samples of a surface run on
-// two ADJACENT LANES instead of one after the other on one thread (lane 2j: the MIS sample, lane 2j+1: the continuation sample
-// and the roulette). Same arithmetic, same RNG dimensions; but a warp now fetches every instruction of the 50 KB sampling
-// code once for 16 surfaces x 2 samples instead of twice for 32 x 1 — instruction-cache misses were this kernel's top stall
-// (r01-w ncu: no_instruction 3.3 cycles per issue at 0.46 IPC). The EC-GGX class draws 2k+1 dimensions per sample (k = scattering
-// orders taken), so its second sample cannot start before the first has finished: it keeps the 2-trip loop.
+// Tried in r02 and dropped: the two samples of a surface on two ADJACENT LANES (lane 2j the MIS sample, lane 2j+1 the continuation)
+// so that a warp fetches each instruction of the 50 KB sampling code once for 16 surfaces x 2 samples — instruction-cache misses are
+// this kernel's top stall. Same bits, but no gain: serial shading 124.5 -> 130 ms per C2 frame (twice the queue reads and surface-record
+// loads, and the two lanes' epilogues diverge).
 template <int INTEG, int CLS>
 __global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
-    constexpr bool PAIRED = INTEG == HJ_INTEGRATOR_MIS && CLS != HJ_CLS_GGX;
-    constexpr uint32_t DRAWS = CLS == HJ_CLS_GLASS ? 1u : 2u;               // RNG calls of one sample of a paired class
-    const uint32_t n = P.cnt->n_cls[CLS] * (PAIRED ? 2u : 1u);
+    const uint32_t n = P.cnt->n_cls[CLS];
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
-        const uint32_t slot = (i < n) ? P.q_cls[CLS][PAIRED ? (i >> 1) : i] : 0xffffffffu;
-        const int k_first = PAIRED ? (int)(i & 1u) : (INTEG == HJ_INTEGRATOR_MIS ? 0 : 1), k_last = PAIRED ? k_first : 1;
+        const uint32_t slot = (i < n) ? P.q_cls[CLS][i] : 0xffffffffu;
         bool push_mis = false, push_next = false;
-        Surface prd; float3 d = f3(0.0f), thr = f3(0.0f); uint32_t rng0 = 0;
-        if (slot != 0xffffffffu) { prd = load_surface(P, slot); d = f3(P.ray_d[slot]); thr = f3(P.thr[slot]); rng0 = P.rng[slot]; }
-        if (PAIRED) __syncwarp();      // a lane pair shares its slot: both lanes have read the slot's state before the second one rewrites it
         if (slot != 0xffffffffu) {
-            Sampler st; st.n_spp = s0 + slot / F.npix; st.scramble = F.frame; st.image_idx = F.pix0 + slot % F.npix; st.depth = rng0;
+            const Surface prd = load_surface(P, slot);
+            const float3 d = f3(P.ray_d[slot]);
+            float3 thr = f3(P.thr[slot]);
+            Sampler st; st.n_spp = s0 + slot / F.npix; st.scramble = F.frame; st.image_idx = F.pix0 + slot % F.npix; st.depth = P.rng[slot];
             if (INTEG != HJ_INTEGRATOR_PT && S.n_lights >= 1) st.depth += 2;     // light pick + barycentrics (light_sample.h:18,60)
             if (INTEG == HJ_INTEGRATOR_MIS && F.sky) st.depth += 1;               // the sky sample's draw (k_nee)
-            if (PAIRED && k_first == 1) st.depth += DRAWS + 1u;                   // the MIS sample's draws and the dead draw (rt.h:426) run on the lane before
             float3 t, b; const float3 nrm = prd.normal;
             onb(nrm, t, b);
             const float3 lwo = to_local(-d, t, nrm, b);
             if (INTEG == HJ_INTEGRATOR_NEE) draw_skip(st);                      // dead draw, rt.h:266
 #pragma unroll 1
-            for (int k = k_first; k <= k_last; k++) {
+            for (int k = (INTEG == HJ_INTEGRATOR_MIS ? 0 : 1); k < 2; k++) {
                 float pdf = 1.0f;                   // defined (reference: uninitialised in MIS)
                 float3 lwi = f3(0.0f, 1.0f, 0.0f);  // defined (reference: uninitialised in MIS)
                 const float3 f = sample_class<CLS>(S, prd, lwo, lwi, pdf, st);
@@ -472,7 +467,8 @@ __global__ void k_accumulate(FrameK F, WfPtrs P, float4* accum, uint32_t s0, uin
     for (uint32_t s = 0; s < n_samples; s++) {
         const size_t slot = (size_t)s * F.npix + idx;
         const float4 L = P.L[slot];
-        a.x += L.x; a.y += L.y; a.z += L.z; a.w += 1.0f;
+        const bool skip = F.nan_repair && !(fabsf(L.x) <= FLT_MAX && fabsf(L.y) <= FLT_MAX && fabsf(L.z) <= FLT_MAX);
+        if (!skip) { a.x += L.x; a.y += L.y; a.z += L.z; a.w += 1.0f; }
         if (F.debug) {
             const size_t o = (size_t)(s0 + s - F.sample_begin) * F.WH + pix;
             path_rad[o] = L; path_ids[o] = P.dbg[slot];
@@ -486,7 +482,9 @@ __global__ void k_finalize(FrameK F, const float4* accum, float4* color, uchar4*
     const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
     if (pix >= F.WH) return;
     const float4 a = accum[pix];
-    const float inv = 1.0f / (float)F.spp;
+    // nan_repair: the mean over the samples that were finite (a.w counts them, summed over ranks); a.w == spp when none was dropped,
+    // so a frame without non-finite samples is the same bits either way
+    const float inv = 1.0f / ((F.nan_repair && a.w > 0.0f) ? a.w : (float)F.spp);
     float3 col = f3(a) * inv;
     if (F.tonemap == HJ_TONEMAP_ACES) col = tonemap_aces(col);
     else if (F.tonemap == HJ_TONEMAP_UCHIMURA) col = tonemap_uchimura(col);
@@ -527,7 +525,7 @@ __global__ void __launch_bounds__(HJ_TRACE_THREADS, HJ_MINB) k_trace_batch(DevSc
 int hj_trace_batch(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, uint32_t* prim_host, float* tuv_host) {
     if (n == 0) return HJ_OK;
     if (n > 0x7fffffffull) { c->err = "hj_trace: at most 2^31-1 rays per call"; return HJ_ERR_INVALID; }
-    DevBuf dr, dp, dt, dc;
+    DevBuf &dr = c->trace_scratch[0], &dp = c->trace_scratch[1], &dt = c->trace_scratch[2], &dc = c->trace_scratch[3];   // kept across calls
     HJ_CUDA(c, dr.reserve(n * 32)); HJ_CUDA(c, dp.reserve(n * 4)); HJ_CUDA(c, dt.reserve(n * 12)); HJ_CUDA(c, dc.reserve(4));
     HJ_CUDA(c, cudaMemcpyAsync(dr.p, rays_host, n * 32, cudaMemcpyHostToDevice, c->stream));
     HJ_CUDA(c, cudaMemsetAsync(dc.p, 0, 4, c->stream));
@@ -539,7 +537,6 @@ int hj_trace_batch(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, u
     if (tuv_host && !any_hit) HJ_CUDA(c, cudaMemcpyAsync(tuv_host, dt.p, n * 12, cudaMemcpyDeviceToHost, c->stream));
     HJ_CUDA(c, cudaStreamSynchronize(c->stream));
     HJ_CUDA(c, cudaGetLastError());
-    dr.release(); dp.release(); dt.release(); dc.release();
     return HJ_OK;
 }
 
@@ -668,7 +665,7 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     F.cright = make_float3(fp->camera_right[0], fp->camera_right[1], fp->camera_right[2]);
     F.cf = fp->camera_f; F.ibl = fp->ibl_intensity;
     F.integrator = fp->integrator; F.max_depth = fp->max_depth; F.tonemap = fp->tonemap; F.jitter = fp->pixel_jitter; F.debug = debug;
-    F.sky = sky ? 1 : 0;
+    F.sky = sky ? 1 : 0; F.nan_repair = c->opt_nan_repair;
 
     int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
     const uint32_t grid = std::min(cdiv_u(cap, WF_THREADS), (uint32_t)sms * 16u);
@@ -770,7 +767,7 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
 
 int hj_wavefront_finalize(hj_ctx* c) {
     const hj_frame_params& fp = c->fp;
-    FrameK F{}; F.W = fp.width; F.H = fp.height; F.WH = fp.width * fp.height; F.spp = fp.spp; F.tonemap = fp.tonemap;
+    FrameK F{}; F.W = fp.width; F.H = fp.height; F.WH = fp.width * fp.height; F.spp = fp.spp; F.tonemap = fp.tonemap; F.nan_repair = c->opt_nan_repair;
     k_finalize<<<cdiv_u(F.WH, 256), 256, 0, c->stream>>>(F, c->aov_accum.as<float4>(), c->aov_color.as<float4>(), c->aov_rgba8.as<uchar4>());
     HJ_CUDA(c, cudaGetLastError());
     return HJ_OK;

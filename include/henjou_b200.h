@@ -175,6 +175,9 @@ const char* hj_last_error(const hj_ctx* ctx);   /* ctx may be NULL: last hj_crea
  *   "paths_per_pass" N (0 = auto), "pipelines" 1..8, "bands" 0 (auto)..64 (pixel bands of a low-spp frame)
  *   "builder" 0 LBVH | 1 PLOC (default), "ploc_tail" 0|1 (last PLOC rounds in one block), "leaf_max" 1..3 (triangles per BVH leaf), "leaf_split" 0|1 (default 1: free
  *   slots of a wide node split multi-triangle leaves), "mis_emitter_first" 0|1, "trace_blocks_per_sm" 0 (auto)..32
+ *   "nan_repair" 0|1 — the ONE option that can change a result, off by default: about one path in 1e8 ends in NaN inside the reference's
+ *   BSDF code (reproduced on purpose); with 1 such samples are left out of their pixel's mean instead of poisoning it (a frame without
+ *   non-finite samples is bit-identical either way)
  *   "verify_accel" 0|1 (also env HJ_VERIFY_ACCEL=1): every hj_accel_build checks the BVH it built (each leaf triangle
  *   inside its slot's box, every primitive in exactly one leaf) and fails with HJ_ERR_INVALID otherwise */
 int hj_set_option(hj_ctx* ctx, const char* key, int64_t value);

@@ -297,3 +297,30 @@ def test_sky_importance_sampling_extension(gpu):
     fpb = hj.frame_params(s, 32, 32, 2, max_depth=4, integrator=abi.INTEGRATOR_MIS, sky_sampling=1, debug_paths=1)
     gpu.render(fpb)
     pt.compare_paths("sky_sampling=1, black 1x1 sky", gpu.readback(abi.AOV_PATH_RADIANCE), gpu.readback(abi.AOV_PATH_IDS), Oracle(s).render(fpb, debug=True), exact=True)
+
+
+def test_nan_repair_option(gpu):
+    """Option nan_repair (off by default: parity): non-finite samples — the reference's BSDF code yields about one per 1e8 paths, here
+    forced by a NaN texel in the sky image — are left out of their pixel's mean instead of poisoning it. Pixels without such a sample
+    are the same bits either way."""
+    from henjou_renderer_b200 import hdrio
+    sky = hdrio.rgbe_to_float4(hdrio.float_to_rgbe(hdrio.procedural_sky(64, 32, seed=4)))
+    sky[10, 20, :3] = np.nan
+    s = scenes.furnace_sphere(metallic=0.0, roughness=0.8, subdiv=3, basecolor=(0.8, 0.8, 0.8))
+    s.set_sky_image(sky)
+    gpu.upload(s); gpu.build_accel()
+    fp = hj.frame_params(s, 96, 96, 8, frame=1, max_depth=5, integrator=abi.INTEGRATOR_MIS)
+    gpu.render(fp)
+    plain = gpu.readback(abi.AOV_COLOR).copy(); acc0 = gpu.readback(abi.AOV_ACCUM).copy()
+    bad = ~np.isfinite(plain[..., :3]).all(-1)
+    assert 0 < bad.mean() < 0.5 and np.all(acc0[..., 3] == 8)
+    gpu.set_option("nan_repair", 1)
+    try:
+        gpu.render(fp)
+        fixed = gpu.readback(abi.AOV_COLOR).copy(); acc1 = gpu.readback(abi.AOV_ACCUM).copy(); rgba = gpu.readback(abi.AOV_RGBA8).copy()
+    finally:
+        gpu.set_option("nan_repair", 0)
+    assert np.isfinite(fixed).all()
+    assert np.array_equal(fixed[~bad].view(np.uint32), plain[~bad].view(np.uint32))        # untouched where nothing was dropped
+    assert np.all(acc1[..., 3][~bad] == 8) and np.all(acc1[..., 3][bad] < 8)                 # the count of samples kept
+    assert rgba[bad][:, :3].max() > 0
