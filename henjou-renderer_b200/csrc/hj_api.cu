@@ -137,7 +137,7 @@ int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
     else if (!strcmp(key, "time_stages")) c->opt_time_stages = value != 0;
     else if (!strcmp(key, "paths_per_pass")) c->opt_paths_per_pass = value;
     else if (!strcmp(key, "trace_blocks_per_sm")) { HJ_REQUIRE(c, value >= 0 && value <= 32, HJ_ERR_INVALID, "hj_set_option: trace_blocks_per_sm must be 0 (auto) .. 32"); c->opt_trace_blocks_per_sm = (int)value; }
-    else if (!strcmp(key, "pipelines")) { HJ_REQUIRE(c, value >= 1 && value <= HJ_MAX_PIPES, HJ_ERR_INVALID, "hj_set_option: pipelines must be 1..8"); c->opt_pipelines = (int)value; }
+    else if (!strcmp(key, "pipelines")) { HJ_REQUIRE(c, value >= 0 && value <= HJ_MAX_PIPES, HJ_ERR_INVALID, "hj_set_option: pipelines must be 0 (auto) .. 8"); c->opt_pipelines = (int)value; }
     else if (!strcmp(key, "builder")) { HJ_REQUIRE(c, value == 0 || value == 1, HJ_ERR_INVALID, "hj_set_option: builder must be 0 (LBVH) or 1 (PLOC)"); c->opt_builder = (int)value; c->bvh.have_topology = false; }
     else if (!strcmp(key, "leaf_max")) { HJ_REQUIRE(c, value >= 1 && value <= 3, HJ_ERR_INVALID, "hj_set_option: leaf_max must be 1..3"); c->opt_leaf_max = (int)value; }
     else if (!strcmp(key, "leaf_split")) c->opt_leaf_split = value != 0;

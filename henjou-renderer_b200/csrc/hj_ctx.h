@@ -82,7 +82,7 @@ struct hj_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_scene = nullptr;   // ev_scene: end of the last hj_scene_upload on `stream`
     std::string err;
     // options
-    int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3, opt_trace_blocks_per_sm = 0, opt_pipelines = 8, opt_builder = 1, opt_mis_emitter_first = 1, opt_leaf_split = 1, opt_verify_accel = 0, opt_bands = 0, opt_ploc_tail = 1;   // builder: 0 Karras radix tree (LBVH), 1 PLOC
+    int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3, opt_trace_blocks_per_sm = 0, opt_pipelines = 0, opt_builder = 1, opt_mis_emitter_first = 1, opt_leaf_split = 1, opt_verify_accel = 0, opt_bands = 0, opt_ploc_tail = 1;   // builder: 0 Karras radix tree (LBVH), 1 PLOC
     int64_t opt_paths_per_pass = 0;
     int opt_nan_repair = 0;       // 0 (default, parity): a non-finite sample poisons its pixel as in the reference; 1: it is left out of the mean
     DevBuf trace_scratch[4];      // hj_trace: rays, primitive ids, (t,b1,b2), queue cursor

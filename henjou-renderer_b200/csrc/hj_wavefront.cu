@@ -48,6 +48,19 @@ struct WfPtrs {
 
 #define WF_THREADS 128
 
+// Path state is touched once per stage and never reused from cache: with HJ_STREAM_STATE the traversal kernels read and write it with
+// the evict-first hints (ld.global.cs / st.global.cs) so that it does not push BVH nodes and triangles out of L1 / L2.
+#ifndef HJ_STREAM_STATE
+#define HJ_STREAM_STATE 1      // r02: C2 380.4 -> 378.0 ms (three runs each), C3 / C5 unchanged
+#endif
+#if HJ_STREAM_STATE
+#define LD_STATE(p) __ldcs(p)
+#define ST_STATE(p, v) __stcs((p), (v))
+#else
+#define LD_STATE(p) (*(p))
+#define ST_STATE(p, v) (*(p) = (v))
+#endif
+
 // warp-aggregated queue push: one atomic per warp; must be reached by all 32 lanes
 HJ_DI void queue_push(uint32_t* counter, uint32_t* queue, bool pred, uint32_t value) {
     const uint32_t m = __ballot_sync(0xffffffffu, pred);
@@ -344,7 +357,7 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S
 #endif
 
 HJ_DI void finish_extend(const FrameK& F, const WfPtrs& P, uint32_t slot, const Hit& h) {
-    P.hit[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.prim));
+    ST_STATE(&P.hit[slot], make_float4(h.t, h.b1, h.b2, __uint_as_float(h.prim)));
     if (F.debug) {                         // L.w = rays traced by this path: only the debug records read it
         float4 L = P.L[slot];
         uint2 g = P.dbg[slot];
@@ -358,18 +371,18 @@ HJ_DI void finish_extend(const FrameK& F, const WfPtrs& P, uint32_t slot, const 
 // TraceOcculution (rt.h:15-41): any hit in (1e-3, dist-1e-3) discards the light sample
 HJ_DI void finish_shadow(const FrameK& F, const WfPtrs& P, uint32_t slot, const Hit& h) {
     if (h.prim != 0xffffffffu && !F.debug) return;         // occluded: nothing to add (the ray count is a debug record)
-    float4 L = P.L[slot];
-    if (h.prim == 0xffffffffu) { const float4 c = P.sh_c[slot]; L.x += c.x; L.y += c.y; L.z += c.z; }
+    float4 L = LD_STATE(&P.L[slot]);
+    if (h.prim == 0xffffffffu) { const float4 c = LD_STATE(&P.sh_c[slot]); L.x += c.x; L.y += c.y; L.z += c.z; }
     L.w += 1.0f;
-    P.L[slot] = L;
+    ST_STATE(&P.L[slot], L);
 }
 // the extra BSDF-sampled ray of MIS (rt.h:383-420): emitter hit weighted by the balance heuristic, sky unweighted
 HJ_DI void finish_mis(const DevScene& S, const FrameK& F, const WfPtrs& P, uint32_t slot, const Hit& h) {
     if (h.prim == HJ_HIT_BLOCKED && !F.debug) return;      // blocked by a non-emitter: no contribution, nothing to load
-    const float4 oq = P.mi_o[slot], dq = P.mi_d[slot], aq = P.mi_a[slot];
-    const float3 org = f3(oq), wi = f3(dq), f = f3(aq), thr = f3(P.mi_t[slot]);
+    const float4 oq = LD_STATE(&P.mi_o[slot]), dq = LD_STATE(&P.mi_d[slot]), aq = LD_STATE(&P.mi_a[slot]);
+    const float3 org = f3(oq), wi = f3(dq), f = f3(aq), thr = f3(LD_STATE(&P.mi_t[slot]));
     const float c1 = oq.w, ppdf = dq.w;
-    const float4 Lq = P.L[slot];
+    const float4 Lq = LD_STATE(&P.L[slot]);
     float3 L = f3(Lq);
     if (h.prim == HJ_HIT_BLOCKED) {
         // emitter-first query (MODE 3): something that is not a light is the closest hit — no contribution (rt.h:394)
@@ -397,7 +410,7 @@ HJ_DI void finish_mis(const DevScene& S, const FrameK& F, const WfPtrs& P, uint3
         } else L += thr * f * c1 * em / ppdf;              // reference: the sky through the BSDF branch, unweighted (rt.h:417-419)
     }
     if (F.debug) { uint2 g = P.dbg[slot]; g.y = (g.y ^ (h.prim + 1u)) * 0x01000193u; P.dbg[slot] = g; }
-    P.L[slot] = f4(L, Lq.w + 1.0f);
+    ST_STATE(&P.L[slot], f4(L, Lq.w + 1.0f));
 }
 
 // the shadow ray of a sky sample (sky_sampling): unoccluded to infinity -> its contribution
@@ -418,10 +431,10 @@ template <int MODE>
 struct WfRayIO {
     const DevScene& S; const FrameK& F; const WfPtrs& P; const uint32_t* __restrict__ queue; uint32_t slot;
     HJ_DI bool load(uint32_t idx, float3& o, float3& d, float& tmin, float& tmax) {
-        slot = queue[idx];
+        slot = LD_STATE(&queue[idx]);
         if (slot == 0xffffffffu) return false;
-        const float4 oq = MODE == 0 ? P.ray_o[slot] : (MODE == 1 ? P.sh_o[slot] : (MODE == 4 ? P.sf0[slot] : P.mi_o[slot]));
-        const float4 dq = MODE == 0 ? P.ray_d[slot] : (MODE == 1 ? P.sh_d[slot] : (MODE == 4 ? P.sk_d[slot] : P.mi_d[slot]));
+        const float4 oq = LD_STATE(MODE == 0 ? &P.ray_o[slot] : (MODE == 1 ? &P.sh_o[slot] : (MODE == 4 ? &P.sf0[slot] : &P.mi_o[slot])));
+        const float4 dq = LD_STATE(MODE == 0 ? &P.ray_d[slot] : (MODE == 1 ? &P.sh_d[slot] : (MODE == 4 ? &P.sk_d[slot] : &P.mi_d[slot])));
         o = f3(oq); d = f3(dq); tmin = 0.001f; tmax = MODE == 1 ? oq.w : 1e16f;
         return true;
     }
@@ -608,7 +621,11 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     const bool debug = fp->debug_paths != 0;
     const bool timed = c->opt_time_stages != 0;
     // passes: whole samples of the whole frame; `np` pipelines keep that many passes in flight (1 when timing stages)
-    int np = timed ? 1 : c->opt_pipelines;
+    // Pipelines in flight. r02 sweep (profiles/r02_summary.md): with the work-stealing traversal the tail of a pass costs little, and
+    // what is left to gain from overlap is bought with smaller passes and 4x the launches. Two pipelines are best at every sample
+    // count from 1 to 64 on C1 / C2 / C5 (C1 16 spp: 9.5 ms with 2, 11.8 with 8; C2 8 spp: 49.8 vs 53.8; 64 spp: 381 vs 386); only
+    // the depth-32 glass scene, whose bounces 10-32 run on tiny queues, still prefers eight (525 vs 533 ms).
+    int np = timed ? 1 : (c->opt_pipelines > 0 ? c->opt_pipelines : (fp->max_depth > 16 ? 8 : 2));
     // Pass size: the persistent traversal kernels keep ~150 k rays in flight and lose lanes while a queue drains, so a
     // pass should be as large as memory allows (r01-i, C2 64 spp: 2 Mi paths 1320, 16 Mi paths 1465 Mrays/s). Auto: the
     // frame split evenly over the pipelines, within half of the free device memory (~220 B of path state per slot).
@@ -686,6 +703,8 @@ int hj_wavefront_render(hj_ctx* c, const hj_frame_params* fp) {
     };
     auto mark_end = [&](cudaStream_t s) { if (timed) cudaEventRecord(c->ev_pool[2 * c->ev_kind.size() - 1], s); };
 
+    // Tried in r02 and dropped: an L2 persisting window (cudaStreamAttributeAccessPolicyWindow) over the BVH nodes. With the carve-out at the
+    // device maximum everything else thrashes (C2 380 -> 514 ms, C5 560 -> 739 ms); sized to the nodes alone (30 MB on C2) it changes nothing.
     HJ_CUDA(c, cudaEventRecord(c->ev0, st));
     HJ_CUDA(c, cudaMemsetAsync(c->aov_accum.p, 0, fb, st));
     for (int p = 0; p < np; p++) HJ_CUDA(c, cudaMemsetAsync(c->wf[p].counters.p, 0, sizeof(WfCounters), st));
