@@ -237,13 +237,13 @@ def gpu_arm(args, rank, world, local_rank):
                            "replicated scene, NCCL all-reduce of accum" if world > 1 else ("single GPU" if args.as_rank_of <= 1 else
                                                                                         "single GPU rendering rank 0's slice of a %d-way strong split" % args.as_rank_of),
                            l2_policy="inputs larger than L2 (126 MB): %d passes of %.1f M paths in flight x ~280 B of path state rewritten every "
-                                     "bounce + %.0f MB of BVH nodes and triangles" % (min(8, r.stats()["passes"]), spp * W * H / max(1, r.stats()["passes"]) / 1e6,
+                                     "bounce + %.0f MB of BVH nodes and triangles" % (r.stats()["passes"], (fp.sample_end - fp.sample_begin) * W * H / max(1, r.stats()["passes"]) / 1e6,
                                                                                      (r.stats()["bvh_nodes"] * r.stats()["bvh_node_bytes"] + scene.n_triangles * 48) / 1e6),
                            timing="CUDA events on the context stream (N=1) / barrier-bracketed wall clock incl. all-reduce, max over ranks (N>1)"),
                spp_per_s=round(int(fp.spp) * args.steps / t_all, 3) if args.as_rank_of <= 1 else None, rays_per_step=rays_all // args.steps,
                render_ms_per_rank_min_max=[round(x, 3) for x in render_ms],
                gpu_launches=launches_all, accel_build_ms=round(accel_ms, 3), accel_first_build_ms=round(accel_cold_ms, 3), clocks=clk, wall_s=round(wall, 3))
-    if world > 1 and strong:
+    if world > 1 and strong and not args.no_weak:
         # the weak-scaling figure beside it: every rank renders the full `spp` samples of a spp*N-sample frame
         tw, rw, _, _, _ = timed(fp_weak, args.steps, 1)
         out["weak"] = dict(value=round(rw / tw / 1e6, 2), unit="Mrays/s", ms_per_step=round(1e3 * tw / args.steps, 3), spp_per_gpu=spp, spp_frame=spp * world)
@@ -377,6 +377,7 @@ def main():
     ap.add_argument("--pageable", action="store_true", help="e2e leg with pageable host buffers (no hj_host_pin)")
     ap.add_argument("--opt", action="append", default=[], help="hj_set_option key=value (repeatable), for A/B runs")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (C5 as BASELINE.json states it: --workload c5 --spp 1024)")
+    ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the extra weak-scaling measurement (long workloads)")
     ap.add_argument("--no-roofline", action="store_true", help="skip the counters / stage-timing passes and the CPU baseline (long workloads)")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="N > 1: split the fixed frame (strong, default) or 64 spp per rank (weak)")
     ap.add_argument("--as-rank-of", type=int, default=1, help="one GPU: render rank 0's slice of an N-way strong split (predicts the split without the box)")
