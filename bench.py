@@ -256,9 +256,7 @@ def gpu_arm(args, rank, world, local_rank):
     pinned = [a for a in (scene.vertices, scene.normals, scene.texcoords, scene.indices, scene.material_ids, color, rgba)
               if a.flags["C_CONTIGUOUS"]] if not args.pageable else []
     r.pin(*pinned)
-    barrier()
-    e_rays, t0 = 0, time.perf_counter()
-    for _ in range(args.steps):
+    def e2e_step():
         if world > 1:
             r.comm_upload(scene, 0)          # hj_comm_scene_upload: one PCIe copy of the geometry on rank 0, ncclBroadcast over NVLink to the others
         else:
@@ -268,7 +266,15 @@ def gpu_arm(args, rank, world, local_rank):
             r.comm_reduce()
         r.sync()
         r.readback(abi.AOV_COLOR, color); r.readback(abi.AOV_RGBA8, rgba)
-        st = r.stats(); e_rays += st["rays_extend"] + st["rays_shadow"]
+        st = r.stats()
+        return st["rays_extend"] + st["rays_shadow"]
+
+    for _ in range(args.e2e_warmup):         # untimed: NCCL sets up the broadcast's connections on first use (8 ranks: ~1 s)
+        e2e_step()
+    barrier()
+    e_rays, t0 = 0, time.perf_counter()
+    for _ in range(args.steps):
+        e_rays += e2e_step()
     barrier()
     e_t = time.perf_counter() - t0
     if world > 1:
@@ -377,6 +383,7 @@ def main():
     ap.add_argument("--pageable", action="store_true", help="e2e leg with pageable host buffers (no hj_host_pin)")
     ap.add_argument("--opt", action="append", default=[], help="hj_set_option key=value (repeatable), for A/B runs")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (C5 as BASELINE.json states it: --workload c5 --spp 1024)")
+    ap.add_argument("--e2e-warmup", type=int, default=1, help="untimed end-to-end steps before the timed ones")
     ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the extra weak-scaling measurement (long workloads)")
     ap.add_argument("--no-roofline", action="store_true", help="skip the counters / stage-timing passes and the CPU baseline (long workloads)")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="N > 1: split the fixed frame (strong, default) or 64 spp per rank (weak)")

@@ -145,6 +145,7 @@ int hj_set_option(hj_ctx* c, const char* key, int64_t value) {
     else if (!strcmp(key, "ploc_tail")) { c->opt_ploc_tail = value != 0; c->bvh.have_topology = false; }
     else if (!strcmp(key, "verify_accel")) c->opt_verify_accel = value != 0;
     else if (!strcmp(key, "nan_repair")) c->opt_nan_repair = value != 0;
+    else if (!strcmp(key, "morton_bits")) { HJ_REQUIRE(c, value >= 4 && value <= 21, HJ_ERR_INVALID, "hj_set_option: morton_bits (per axis) must be 4..21"); c->opt_morton_bits = (int)value; c->bvh.have_topology = false; }
     else if (!strcmp(key, "mis_emitter_first")) c->opt_mis_emitter_first = value != 0;
     else if (!strcmp(key, "denoise_iterations")) { HJ_REQUIRE(c, value >= 0 && value <= 8, HJ_ERR_INVALID, "hj_set_option: denoise_iterations must be 0..8"); c->opt_denoise_iterations = (int)value; }
     else if (!strncmp(key, "denoise_sigma_", 14)) {

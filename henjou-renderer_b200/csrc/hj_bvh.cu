@@ -74,7 +74,7 @@ HJ_DI uint64_t spread21(uint32_t v) {
     return x;
 }
 
-__global__ void k_morton(DevScene S, const int* bounds, uint64_t* keys, uint32_t* vals) {
+__global__ void k_morton(DevScene S, const int* bounds, uint64_t* keys, uint32_t* vals, int drop_bits) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= S.n_tris) return;
     const float3 lo = f3(ord2f(bounds[0]), ord2f(bounds[1]), ord2f(bounds[2]));
@@ -88,7 +88,8 @@ __global__ void k_morton(DevScene S, const int* bounds, uint64_t* keys, uint32_t
     const uint32_t qx = (uint32_t)fminf(fmaxf((cen.x - lo.x) / e * 2097152.0f, 0.0f), 2097151.0f);
     const uint32_t qy = (uint32_t)fminf(fmaxf((cen.y - lo.y) / e * 2097152.0f, 0.0f), 2097151.0f);
     const uint32_t qz = (uint32_t)fminf(fmaxf((cen.z - lo.z) / e * 2097152.0f, 0.0f), 2097151.0f);
-    keys[t] = (spread21(qx) << 2) | (spread21(qy) << 1) | spread21(qz);
+    // option morton_bits: the low `drop_bits` of every axis are dropped, so the key has 3 x (21 - drop_bits) bits and the sort needs fewer passes
+    keys[t] = (spread21(qx >> drop_bits) << 2) | (spread21(qy >> drop_bits) << 1) | spread21(qz >> drop_bits);
     vals[t] = t;
 }
 
@@ -812,14 +813,19 @@ int hj_bvh_enqueue(hj_ctx* c, const float* xf, const float* inv_xf, int mode) {
         HJ_CUDA(c, B.block_hist.reserve((size_t)256 * nb * 4)); HJ_CUDA(c, B.digit_total.reserve(256 * 4));
         HJ_CUDA(c, B.left.reserve((size_t)n * 4)); HJ_CUDA(c, B.right.reserve((size_t)n * 4));
         HJ_CUDA(c, B.parent.reserve(2 * (size_t)n * 4));
-        k_morton<<<cdiv(n, 256), 256, 0, st>>>(S, B.bounds.as<int>(), B.keys.as<uint64_t>(), B.vals.as<uint32_t>());
+        const int bpa = c->opt_morton_bits, key_bits = 3 * bpa, n_passes = (key_bits + 7) / 8;
+        k_morton<<<cdiv(n, 256), 256, 0, st>>>(S, B.bounds.as<int>(), B.keys.as<uint64_t>(), B.vals.as<uint32_t>(), 21 - bpa);
         uint64_t *k0 = B.keys.as<uint64_t>(), *k1 = B.keys_alt.as<uint64_t>();
         uint32_t *v0 = B.vals.as<uint32_t>(), *v1 = B.vals_alt.as<uint32_t>();
-        for (int pass = 0; pass < 8; pass++) {      // 63-bit keys: 8 passes of 8 bits, result back in k0/v0
+        for (int pass = 0; pass < n_passes; pass++) {      // 8 bits per pass over the populated key bits
             k_rs_hist<<<nb, RS_THREADS, 0, st>>>(k0, n, 8 * pass, B.block_hist.as<uint32_t>(), nb);
             k_rs_scan_rows<<<256, RS_SCAN_THREADS, 0, st>>>(B.block_hist.as<uint32_t>(), nb, B.digit_total.as<uint32_t>());
             k_rs_scatter<<<nb, RS_THREADS, 0, st>>>(k0, v0, n, 8 * pass, B.block_hist.as<uint32_t>(), B.digit_total.as<uint32_t>(), nb, k1, v1);
             std::swap(k0, k1); std::swap(v0, v1);
+        }
+        if (n_passes & 1) {         // an odd number of passes leaves the result in the alternate buffers: the tree builders read B.keys / B.vals
+            HJ_CUDA(c, cudaMemcpyAsync(B.keys.p, B.keys_alt.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+            HJ_CUDA(c, cudaMemcpyAsync(B.vals.p, B.vals_alt.p, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
         }
         HJ_CUDA(c, B.cnt.reserve((size_t)n * 4));
         HJ_CUDA(c, B.blo.reserve(2 * (size_t)n * sizeof(float4))); HJ_CUDA(c, B.bhi.reserve(2 * (size_t)n * sizeof(float4)));

@@ -84,6 +84,7 @@ struct hj_ctx {
     // options
     int opt_count_fetches = 0, opt_time_stages = 0, opt_leaf_max = 3, opt_trace_blocks_per_sm = 0, opt_pipelines = 0, opt_builder = 1, opt_mis_emitter_first = 1, opt_leaf_split = 1, opt_verify_accel = 0, opt_bands = 0, opt_ploc_tail = 1;   // builder: 0 Karras radix tree (LBVH), 1 PLOC
     int64_t opt_paths_per_pass = 0;
+    int opt_morton_bits = 21;     // Morton bits per axis (21: 63-bit keys, 8 sort passes; 16: 6 passes; 13: 5; 10: 4)
     int opt_nan_repair = 0;       // 0 (default, parity): a non-finite sample poisons its pixel as in the reference; 1: it is left out of the mean
     DevBuf trace_scratch[4];      // hj_trace: rays, primitive ids, (t,b1,b2), queue cursor
     // scene
