@@ -34,8 +34,12 @@ HJ_DI float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
 // ≙ the vertex fetch + transform of __closesthit__ch (stale PTX :880-1287) hoisted out of the hit program:
 // p_k = transform_position(transforms[inst], vertices[i_k]); n_k = normalize(transform_normal(inv[inst], normals[i_k]))
-__global__ void k_flatten(DevScene S, int* bounds, uint32_t* error) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+#define FLATTEN_THREADS 256
+__global__ void __launch_bounds__(FLATTEN_THREADS) k_flatten(DevScene S, int* bounds, uint32_t* error) {
+    // the 7 float4 a triangle produces are staged in shared memory and written out by the whole block: 48-B / 64-B records written by
+    // one thread each are strided 16-B stores (r02: 1.70 ms for the 10.2 M triangles of C5 against 0.36 ms of pure traffic)
+    __shared__ float4 s_pos[3 * FLATTEN_THREADS], s_attr[4 * FLATTEN_THREADS];
+    const uint32_t t0 = blockIdx.x * FLATTEN_THREADS, t = t0 + threadIdx.x;
     float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     if (t < S.n_tris) {
         const uint32_t inst = S.tri_inst[t];
@@ -50,12 +54,17 @@ __global__ void k_flatten(DevScene S, int* bounds, uint32_t* error) {
             lo[0] = fminf(lo[0], p[k].x); lo[1] = fminf(lo[1], p[k].y); lo[2] = fminf(lo[2], p[k].z);
             hi[0] = fmaxf(hi[0], p[k].x); hi[1] = fmaxf(hi[1], p[k].y); hi[2] = fmaxf(hi[2], p[k].z);
         }
-        float4* P = S.tri_pos + 3 * (size_t)t;
+        float4* P = s_pos + 3 * threadIdx.x;
         P[0] = f4(p[0], 0.0f); P[1] = f4(p[1], 0.0f); P[2] = f4(p[2], 0.0f);
-        float4* A = S.tri_attr + 4 * (size_t)t;
+        float4* A = s_attr + 4 * threadIdx.x;
         A[0] = f4(n[0], uv[0].x); A[1] = f4(n[1], uv[0].y); A[2] = f4(n[2], uv[1].x);
         A[3] = make_float4(uv[1].y, uv[2].x, uv[2].y, __uint_as_float(S.material_ids[t]));
     }
+    __syncthreads();
+    const uint32_t n_here = min((uint32_t)FLATTEN_THREADS, S.n_tris > t0 ? S.n_tris - t0 : 0u);
+    float4* Pg = S.tri_pos + 3 * (size_t)t0; float4* Ag = S.tri_attr + 4 * (size_t)t0;
+    for (uint32_t i = threadIdx.x; i < 3 * n_here; i += FLATTEN_THREADS) Pg[i] = s_pos[i];
+    for (uint32_t i = threadIdx.x; i < 4 * n_here; i += FLATTEN_THREADS) Ag[i] = s_attr[i];
     // block reduction of the scene bounds, one atomic per warp
     for (int a = 0; a < 3; a++) {
         float l = lo[a], h = hi[a];
@@ -803,7 +812,7 @@ int hj_bvh_enqueue(hj_ctx* c, const float* xf, const float* inv_xf, int mode) {
     HJ_CUDA(c, cudaMemcpyAsync(A.xf.p, m, 48 * (size_t)n_inst, cudaMemcpyHostToDevice, st));
     HJ_CUDA(c, cudaMemcpyAsync(A.inv_xf.p, im, 48 * (size_t)n_inst, cudaMemcpyHostToDevice, st));
     k_build_begin<<<1, 32, 0, st>>>(dst, B.bounds.as<int>());
-    k_flatten<<<cdiv(n, 256), 256, 0, st>>>(S, B.bounds.as<int>(), &dst->error);
+    k_flatten<<<cdiv(n, FLATTEN_THREADS), FLATTEN_THREADS, 0, st>>>(S, B.bounds.as<int>(), &dst->error);
     const bool topo = (mode == HJ_ACCEL_BUILD) || !B.have_topology;
     uint32_t root = 0;
     if (topo) {
