@@ -164,7 +164,7 @@ HJ_DI float light_pdf_area(const DevScene& S, uint32_t prim) {
 // Every stage derives its RNG dimension from the counter stored at the start of the iteration, so the draw order of
 // SURVEY §8 "draw ledger" is unchanged: [light pick, light barycentrics] [MIS sample] [dead] [continuation] [roulette].
 #ifndef HJ_SHADE_MINB
-#define HJ_SHADE_MINB 6
+#define HJ_SHADE_MINB 8       // 64 registers. r02 (after the shared double-precision libm): C2 379.3 -> 376.1 ms against 6 blocks / 80 registers
 #endif
 #ifndef HJ_SURF_MINB
 #define HJ_SURF_MINB HJ_SHADE_MINB

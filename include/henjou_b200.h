@@ -173,7 +173,7 @@ const char* hj_last_error(const hj_ctx* ctx);   /* ctx may be NULL: last hj_crea
 /* Tuning / diagnostic options (none changes a result):
  *   "count_fetches" 0|1, "time_stages" 0|1       counters pass / serial event-pair timing of the stages (hj_stats)
  *   "paths_per_pass" N (0 = auto), "pipelines" 0 (auto: 2, or 8 beyond depth 16) .. 8, "bands" 0 (auto)..64 (pixel bands of a low-spp frame)
- *   "builder" 0 LBVH | 1 PLOC (default), "ploc_tail" 0|1 (last PLOC rounds in one block), "leaf_max" 1..3 (triangles per BVH leaf), "leaf_split" 0|1 (default 1: free
+ *   "morton_bits" 4..21 per axis (default 10: 30-bit codes, 4 radix passes), "builder" 0 LBVH | 1 PLOC (default), "ploc_tail" 0|1 (last PLOC rounds in one block), "leaf_max" 1..3 (triangles per BVH leaf), "leaf_split" 0|1 (default 1: free
  *   slots of a wide node split multi-triangle leaves), "mis_emitter_first" 0|1, "trace_blocks_per_sm" 0 (auto)..32
  *   "nan_repair" 0|1 — the ONE option that can change a result, off by default: about one path in 1e8 ends in NaN inside the reference's
  *   BSDF code (reproduced on purpose); with 1 such samples are left out of their pixel's mean instead of poisoning it (a frame without
