@@ -272,9 +272,11 @@ def gpu_arm(args, rank, world, local_rank):
     for _ in range(args.e2e_warmup):         # untimed: NCCL sets up the broadcast's connections on first use (8 ranks: ~1 s)
         e2e_step()
     barrier()
-    e_rays, t0 = 0, time.perf_counter()
+    e_rays, t0, e_steps = 0, time.perf_counter(), []
     for _ in range(args.steps):
+        ts = time.perf_counter()
         e_rays += e2e_step()
+        e_steps.append(round(1e3 * (time.perf_counter() - ts), 2))
     barrier()
     e_t = time.perf_counter() - t0
     if world > 1:
@@ -286,7 +288,7 @@ def gpu_arm(args, rank, world, local_rank):
     small = scene.prim_offsets.nbytes + xf.nbytes + inv.nbytes + (scene.lut.nbytes if scene.lut is not None else 0) + scene.ibl.nbytes
     out["e2e"] = dict(value=round(e_rays / e_t / 1e6, 2), unit="Mrays/s", h2d_bytes_per_step=int(h2d) + int(small) * (world - 1), d2h_bytes_per_step=int(d2h) * world,
                       nvlink_broadcast_bytes_per_step=int(h2d - small) * (world - 1) if world > 1 else 0,
-                      ms_per_step=round(1e3 * e_t / args.steps, 3), checksum=float(np.nanmean(np.where(np.isfinite(color[..., :3]), color[..., :3], np.nan))),
+                      ms_per_step=round(1e3 * e_t / args.steps, 3), ms_steps_rank0=e_steps, checksum=float(np.nanmean(np.where(np.isfinite(color[..., :3]), color[..., :3], np.nan))),
                       non_finite_pixels=int((~np.isfinite(color[..., :3]).all(-1)).sum()),
                       host_memory="pageable" if args.pageable else "pinned (hj_host_pin)")
     r.unpin(*pinned)

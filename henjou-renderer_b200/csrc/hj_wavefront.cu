@@ -5,8 +5,8 @@
 //
 // One path per slot; slot = s_local * W*H + pixel, so the RNG stream of a path is CMJState{n_spp = global sample
 // index, scramble = frame, image_idx = pixel} regardless of how samples are sliced over passes or GPUs.
-// Per bounce:   k_trace<0> (closest hit)  ->  k_surface (closest-hit / miss programs, sort into BSDF-class queues)  ->  k_nee
-// (light sample + BSDF evaluation -> shadow queue)  ->  k_sample<class> (MIS sample -> MIS queue, continuation sample, Russian
+// Per bounce:   k_trace<0> (closest hit)  ->  k_surface (closest-hit / miss programs, sort into BSDF-class queues)  ->
+// k_sample<class> (light sample + BSDF evaluation -> shadow queue; MIS sample -> MIS queue; continuation sample, Russian
 // roulette -> next-bounce queue; warp-aggregated pushes)  ->  k_trace<1> (any hit)  ->  k_trace<3> (MIS emitter ray). Queue
 // lengths live in device memory and every kernel is a grid-stride loop over its queue, so a frame is enqueued without a single
 // host synchronisation.
@@ -159,8 +159,8 @@ HJ_DI float light_pdf_area(const DevScene& S, uint32_t prim) {
 // k_shade ran at 0.32 IPC with instruction-cache misses as its top stall and 15 of 32 lanes (r01-g) — straight-line code
 // executed once per path has no reuse in the 6 KB L0 / 32 KB L1.5 instruction caches. Stages:
 //   k_surface          closest-hit / miss programs: sky, emitter hits, AOVs, surface record, sort into class queues
-//   k_nee<INTEG>       light sample + BSDF evaluation -> shadow ray               (non-specular surfaces)
-//   k_sample<INTEG,C>  MIS BSDF sample -> MIS ray; dead draw; continuation sample; roulette   (one class C per launch)
+//   k_sample<INTEG,C>  light sample + BSDF evaluation -> shadow ray (non-specular classes; a kernel of its own, k_nee, until r02);
+//                      MIS BSDF sample -> MIS ray; dead draw; continuation sample; roulette   (one class C per launch)
 // Every stage derives its RNG dimension from the counter stored at the start of the iteration, so the draw order of
 // SURVEY §8 "draw ledger" is unchanged: [light pick, light barycentrics] [MIS sample] [dead] [continuation] [roulette].
 #ifndef HJ_SHADE_MINB
@@ -223,66 +223,52 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SURF_MINB) k_surface(DevScene S
         queue_push(&P.cnt->n_cls[HJ_CLS_DISNEY], P.q_cls[HJ_CLS_DISNEY], cls == HJ_CLS_DISNEY, slot);
         queue_push(&P.cnt->n_cls[HJ_CLS_GGX], P.q_cls[HJ_CLS_GGX], cls == HJ_CLS_GGX, slot);
         queue_push(&P.cnt->n_cls[HJ_CLS_GLASS], P.q_cls[HJ_CLS_GLASS], cls == HJ_CLS_GLASS, slot);
-        if (INTEG != HJ_INTEGRATOR_PT) queue_push(&P.cnt->n_ns, P.q_ns, cls == HJ_CLS_DISNEY || cls == HJ_CLS_GGX, slot);
     }
 }
 
-// light sampling + BSDF evaluation of the non-specular surfaces (rt.h:219-260 / 341-380). Specular surfaces evaluate to
-// zero (BSDFs.h:1006-1013), so their light sample contributes nothing and only moves the RNG counter (k_sample skips it).
+// Light sampling + BSDF evaluation at a non-specular surface (rt.h:219-260 / 341-380): the first part of a loop iteration after the
+// closest hit. Specular surfaces evaluate to zero (BSDFs.h:1006-1013), so their light sample contributes nothing and only moves the
+// RNG counter. r02: this ran as a kernel of its own (k_nee) between k_surface and k_sample, re-reading the 64-B surface record, the ray
+// and the throughput that k_sample reads again; it is now the head of k_sample (same draws, same arithmetic, one pass over the state).
 template <int INTEG>
-__global__ void __launch_bounds__(WF_THREADS, HJ_NEE_MINB) k_nee(DevScene S, FrameK F, WfPtrs P, uint32_t s0) {
-    const uint32_t n = P.cnt->n_ns;
-    const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
-        const uint32_t slot = (i < n) ? P.q_ns[i] : 0xffffffffu;
-        bool push_shadow = false, push_sky = false;
-        if (slot != 0xffffffffu) {
-            const Surface prd = load_surface(P, slot);
-            const float3 d = f3(P.ray_d[slot]), thr = f3(P.thr[slot]);
-            Sampler st; st.n_spp = s0 + slot / F.npix; st.scramble = F.frame; st.image_idx = F.pix0 + slot % F.npix; st.depth = P.rng[slot];
-            Disney bsdf; bsdf.init(prd);
-            float3 t, b; const float3 nrm = prd.normal;
-            onb(nrm, t, b);
-            const float3 lwo = to_local(-d, t, nrm, b);
-            if (S.n_lights >= 1) {
-                float lpdf; float3 lnrm, lem;
-                const float3 lpos = sample_light(S, st, lpdf, lnrm, lem);
-                float3 ld = lpos - prd.position;
-                const float dist = length(ld);
-                ld = normalize(ld);
-                const float c1 = absdot(nrm, ld), c2 = absdot(lnrm, -ld);
-                const float3 lwi = to_local(ld, t, nrm, b);
-                const float3 f = bsdf.eval(S, lwo, lwi);
-                const float G = c2 / (dist * dist);
-                float3 contrib;
-                if (INTEG == HJ_INTEGRATOR_MIS) {
-                    const float ppdf = bsdf.pdf(lwo, lwi) * G;
-                    const float w = lpdf / (lpdf + ppdf);
-                    contrib = thr * (f * G * c1 / lpdf) * w * lem;
-                } else contrib = thr * (f * G * c1 / lpdf) * lem;
-                if (!is_zero3(contrib)) {
-                    push_shadow = true;
-                    P.sh_o[slot] = f4(prd.position, dist - 0.001f); P.sh_d[slot] = f4(ld, 0.0f); P.sh_c[slot] = f4(contrib, 0.0f);
-                }
-            }
-            if (INTEG == HJ_INTEGRATOR_MIS && F.sky) {
-                // extension (sky_sampling): one direction drawn from the sky's luminance table, balance heuristic against the BSDF
-                // pdf; the matching weight on BSDF-sampled rays that reach the sky is applied in finish_mis
-                const float2 xi = draw2(st);
-                float spdf;
-                const float3 sd = sky_sample(S, xi, spdf);
-                if (spdf > 0.0f) {
-                    const float c1 = absdot(nrm, sd);
-                    const float3 lwi = to_local(sd, t, nrm, b);
-                    const float3 f = bsdf.eval(S, lwo, lwi);
-                    const float w = spdf / (spdf + bsdf.pdf(lwo, lwi));
-                    const float3 contrib = thr * (f * c1 / spdf) * w * sky_radiance(S, sd, F.ibl);
-                    if (!is_zero3(contrib)) { push_sky = true; P.sk_d[slot] = f4(sd, 0.0f); P.sk_c[slot] = f4(contrib, 0.0f); }
-                }
-            }
+HJ_DI void nee_stage(const DevScene& S, const FrameK& F, const WfPtrs& P, uint32_t slot, const Surface& prd, const float3& thr, const float3& lwo,
+                     const float3& t, const float3& nrm, const float3& b, Sampler& st, bool& push_shadow, bool& push_sky) {
+    Disney bsdf; bsdf.init(prd);
+    if (S.n_lights >= 1) {
+        float lpdf; float3 lnrm, lem;
+        const float3 lpos = sample_light(S, st, lpdf, lnrm, lem);
+        float3 ld = lpos - prd.position;
+        const float dist = length(ld);
+        ld = normalize(ld);
+        const float c1 = absdot(nrm, ld), c2 = absdot(lnrm, -ld);
+        const float3 lwi = to_local(ld, t, nrm, b);
+        const float3 f = bsdf.eval(S, lwo, lwi);
+        const float G = c2 / (dist * dist);
+        float3 contrib;
+        if (INTEG == HJ_INTEGRATOR_MIS) {
+            const float ppdf = bsdf.pdf(lwo, lwi) * G;
+            const float w = lpdf / (lpdf + ppdf);
+            contrib = thr * (f * G * c1 / lpdf) * w * lem;
+        } else contrib = thr * (f * G * c1 / lpdf) * lem;
+        if (!is_zero3(contrib)) {
+            push_shadow = true;
+            P.sh_o[slot] = f4(prd.position, dist - 0.001f); P.sh_d[slot] = f4(ld, 0.0f); P.sh_c[slot] = f4(contrib, 0.0f);
         }
-        queue_push(&P.cnt->n_shadow, P.q_shadow, push_shadow, slot);
-        if (INTEG == HJ_INTEGRATOR_MIS && F.sky) queue_push(&P.cnt->n_sky, P.q_sky, push_sky, slot);
+    }
+    if (INTEG == HJ_INTEGRATOR_MIS && F.sky) {
+        // extension (sky_sampling): one direction drawn from the sky's luminance table, balance heuristic against the BSDF
+        // pdf; the matching weight on BSDF-sampled rays that reach the sky is applied in finish_mis
+        const float2 xi = draw2(st);
+        float spdf;
+        const float3 sd = sky_sample(S, xi, spdf);
+        if (spdf > 0.0f) {
+            const float c1 = absdot(nrm, sd);
+            const float3 lwi = to_local(sd, t, nrm, b);
+            const float3 f = bsdf.eval(S, lwo, lwi);
+            const float w = spdf / (spdf + bsdf.pdf(lwo, lwi));
+            const float3 contrib = thr * (f * c1 / spdf) * w * sky_radiance(S, sd, F.ibl);
+            if (!is_zero3(contrib)) { push_sky = true; P.sk_d[slot] = f4(sd, 0.0f); P.sk_c[slot] = f4(contrib, 0.0f); }
+        }
     }
 }
 
@@ -307,17 +293,20 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
         const uint32_t slot = (i < n) ? P.q_cls[CLS][i] : 0xffffffffu;
-        bool push_mis = false, push_next = false;
+        bool push_mis = false, push_next = false, push_shadow = false, push_sky = false;
         if (slot != 0xffffffffu) {
             const Surface prd = load_surface(P, slot);
             const float3 d = f3(P.ray_d[slot]);
             float3 thr = f3(P.thr[slot]);
             Sampler st; st.n_spp = s0 + slot / F.npix; st.scramble = F.frame; st.image_idx = F.pix0 + slot % F.npix; st.depth = P.rng[slot];
-            if (INTEG != HJ_INTEGRATOR_PT && S.n_lights >= 1) st.depth += 2;     // light pick + barycentrics (light_sample.h:18,60)
-            if (INTEG == HJ_INTEGRATOR_MIS && F.sky) st.depth += 1;               // the sky sample's draw (k_nee)
             float3 t, b; const float3 nrm = prd.normal;
             onb(nrm, t, b);
             const float3 lwo = to_local(-d, t, nrm, b);
+            if (INTEG != HJ_INTEGRATOR_PT && CLS != HJ_CLS_GLASS) nee_stage<INTEG>(S, F, P, slot, prd, thr, lwo, t, nrm, b, st, push_shadow, push_sky);
+            else {                                                               // specular: the draws are made, their values never used
+                if (INTEG != HJ_INTEGRATOR_PT && S.n_lights >= 1) st.depth += 2;   // light pick + barycentrics (light_sample.h:18,60)
+                if (INTEG == HJ_INTEGRATOR_MIS && F.sky) st.depth += 1;             // the sky sample's draw
+            }
             if (INTEG == HJ_INTEGRATOR_NEE) draw_skip(st);                      // dead draw, rt.h:266
 #pragma unroll 1
             for (int k = (INTEG == HJ_INTEGRATOR_MIS ? 0 : 1); k < 2; k++) {
@@ -343,6 +332,8 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S
                 }
             }
         }
+        if (INTEG != HJ_INTEGRATOR_PT && CLS != HJ_CLS_GLASS) queue_push(&P.cnt->n_shadow, P.q_shadow, push_shadow, slot);
+        if (INTEG == HJ_INTEGRATOR_MIS && CLS != HJ_CLS_GLASS && F.sky) queue_push(&P.cnt->n_sky, P.q_sky, push_sky, slot);
         if (INTEG == HJ_INTEGRATOR_MIS) queue_push(&P.cnt->n_mis, P.q_mis, push_mis, slot);
         queue_push(&P.cnt->n_extend[cur ^ 1], P.q_ext[cur ^ 1], push_next, slot);
     }
@@ -564,7 +555,6 @@ static int wf_reserve(hj_ctx* c, WavefrontState& w, uint32_t cap, bool mis, bool
     HJ_CUDA(c, w.q_extend[0].reserve((size_t)cap * 4)); HJ_CUDA(c, w.q_extend[1].reserve((size_t)cap * 4));
     HJ_CUDA(c, w.q_shadow.reserve((size_t)cap * 4)); HJ_CUDA(c, w.q_mis.reserve((size_t)cap * 4));
     for (int k = 0; k < 3; k++) HJ_CUDA(c, w.q_cls[k].reserve((size_t)cap * 4));
-    HJ_CUDA(c, w.q_ns.reserve((size_t)cap * 4));
     for (int k = 0; k < 4; k++) HJ_CUDA(c, w.sf[k].reserve(f4s));
     HJ_CUDA(c, w.sh_o.reserve(f4s)); HJ_CUDA(c, w.sh_d.reserve(f4s)); HJ_CUDA(c, w.sh_c.reserve(f4s));
     if (mis) { HJ_CUDA(c, w.mi_o.reserve(f4s)); HJ_CUDA(c, w.mi_d.reserve(f4s)); HJ_CUDA(c, w.mi_a.reserve(f4s)); HJ_CUDA(c, w.mi_t.reserve(f4s)); }
@@ -598,7 +588,6 @@ template <int INTEG>
 static int launch_shade_t(hj_ctx* c, uint32_t grid, cudaStream_t ps, const FrameK& F, const WfPtrs& P, int cur, int depth, uint32_t s0) {
     int n = 4;
     k_surface<INTEG><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
-    if (INTEG != HJ_INTEGRATOR_PT && (c->S.n_lights >= 1 || (INTEG == HJ_INTEGRATOR_MIS && F.sky))) { k_nee<INTEG><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, s0); n++; }
     k_sample<INTEG, HJ_CLS_DISNEY><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
     k_sample<INTEG, HJ_CLS_GGX><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
     k_sample<INTEG, HJ_CLS_GLASS><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
