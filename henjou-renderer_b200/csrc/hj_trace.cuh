@@ -190,7 +190,7 @@ HJ_DI void fill_octant_perm(uint8_t (*perm)[256]) {
 #define STEAL_MIN_IDLE 1     // idle lanes before a warp steals (r01-w sweep 1/16/24: 1 is best on C2, C3 and C5)
 #endif
 #ifndef TRI_K
-#define TRI_K 2              // a batch runs once pending pairs >= min(32, TRI_K x lanes doing node work)
+#define TRI_K 1              // a batch runs once pending pairs >= min(32, TRI_K x lanes doing node work). r02 sweep: 1 beats 2 by 0.9 % (C2, C3), 1.3 % (C5)
 #endif
 
 template <int QUERY>
