@@ -200,6 +200,8 @@ def gpu_arm(args, rank, world, local_rank):
             r.comm_reduce()          # NCCL all-reduce of the accumulation buffer + finalize (syncs the stream)
         r.sync()
 
+    step_wall = []
+
     def timed(fp, steps, warmup):
         """-> (seconds: max over ranks, rays: sum over ranks, launches: sum over ranks, wall, per-rank device ms list)"""
         for _ in range(warmup):
@@ -207,8 +209,11 @@ def gpu_arm(args, rank, world, local_rank):
         barrier()
         t0 = time.perf_counter()
         dev_ms, rays, launches = 0.0, 0, 0
+        step_wall.clear()
         for _ in range(steps):
+            ts = time.perf_counter()
             step(fp)
+            step_wall.append(round(1e3 * (time.perf_counter() - ts), 3))
             st = r.stats()
             dev_ms += st["ms_render"]; rays += st["rays_extend"] + st["rays_shadow"]; launches += st["kernel_launches"]
         barrier()
@@ -241,7 +246,7 @@ def gpu_arm(args, rank, world, local_rank):
                                                                                      (r.stats()["bvh_nodes"] * r.stats()["bvh_node_bytes"] + scene.n_triangles * 48) / 1e6),
                            timing="CUDA events on the context stream (N=1) / barrier-bracketed wall clock incl. all-reduce, max over ranks (N>1)"),
                spp_per_s=round(int(fp.spp) * args.steps / t_all, 3) if args.as_rank_of <= 1 else None, rays_per_step=rays_all // args.steps,
-               render_ms_per_rank_min_max=[round(x, 3) for x in render_ms],
+               render_ms_per_rank_min_max=[round(x, 3) for x in render_ms], step_wall_ms_rank0=list(step_wall),
                gpu_launches=launches_all, accel_build_ms=round(accel_ms, 3), accel_first_build_ms=round(accel_cold_ms, 3), clocks=clk, wall_s=round(wall, 3))
     if world > 1 and strong and not args.no_weak:
         # the weak-scaling figure beside it: every rank renders the full `spp` samples of a spp*N-sample frame
