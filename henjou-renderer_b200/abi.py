@@ -71,5 +71,7 @@ EXPORTS = [
     "hj_abi_version", "hj_create", "hj_destroy", "hj_last_error", "hj_set_option", "hj_scene_upload",
     "hj_accel_build", "hj_render", "hj_render_async", "hj_sync", "hj_readback", "hj_device_ptr",
     "hj_finalize", "hj_get_stats", "hj_comm_unique_id", "hj_comm_init", "hj_comm_reduce", "hj_trace",
-    "hj_host_pin", "hj_host_unpin", "hj_post", "hj_libm_eval", "hj_accel_build_async", "hj_accel_wait", "hj_comm_scene_upload",
+    "hj_host_pin", "hj_host_unpin", "hj_post", "hj_libm_eval", "hj_accel_build_async", "hj_accel_wait", "hj_comm_scene_upload", "hj_trace_noalloc",
 ]
+
+TRACE_NOALLOC_MAX_RAYS = 65536      # HJ_TRACE_NOALLOC_MAX_RAYS (include/henjou_b200.h)

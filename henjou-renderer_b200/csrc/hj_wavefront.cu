@@ -14,6 +14,7 @@
 // reference loop exactly; rays whose contribution is exactly zero are not traced (they cannot change the result).
 #include "hj_ctx.h"
 #include <cstdlib>
+#include <mutex>
 #include "hj_bsdf.cuh"
 #include "hj_trace.cuh"
 
@@ -539,6 +540,61 @@ int hj_trace_batch(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, u
     else k_trace_batch<false><<<grid, HJ_TRACE_THREADS, 0, c->stream>>>(c->S, dr.as<float4>(), (uint32_t)n, dp.as<uint32_t>(), dt.as<float>(), dc.as<uint32_t>());
     if (prim_host) HJ_CUDA(c, cudaMemcpyAsync(prim_host, dp.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
     if (tuv_host && !any_hit) HJ_CUDA(c, cudaMemcpyAsync(tuv_host, dt.p, n * 12, cudaMemcpyDeviceToHost, c->stream));
+    HJ_CUDA(c, cudaStreamSynchronize(c->stream));
+    HJ_CUDA(c, cudaGetLastError());
+    return HJ_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- hj_trace_noalloc
+// hj_trace for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it). No counterpart in the reference. The scratch memory that hj_trace_batch keeps
+// in DevBufs (device staging of the rays and of the results, and the work-fetch cursor of the persistent kernel) lives in ONE
+// file-scope device array of a fixed, modest size; every GPU that loads the library holds it until the process exits.
+//   layout: [0, 256) cursor (uint32, cleared before every launch) | rays 32 B x MAX | prim 4 B x MAX | (t,b1,b2) 12 B x MAX
+// In HOST code the array's name is a host-side stand-in, not a device address: its device address is looked up once per device,
+// with that device current, by cudaGetSymbolAddress, and that pointer is what the kernel gets. All calls share the array and it
+// keeps the last call's contents: the cursor is cleared per call, every result slot below n is written by the kernel, and calls
+// that overlap on one GPU (two contexts / streams / threads) race on it.
+#define HJ_NOALLOC_BYTES (256 + (size_t)HJ_TRACE_NOALLOC_MAX_RAYS * (32 + 4 + 12))
+static __device__ __align__(256) unsigned char g_trace_noalloc_scratch[HJ_NOALLOC_BYTES];
+#define HJ_NOALLOC_MAX_DEVICES 64
+static unsigned char* g_trace_noalloc_ptr[HJ_NOALLOC_MAX_DEVICES];      // device address of the array, per device (0 = not looked up yet)
+static std::mutex g_trace_noalloc_mutex;
+
+extern "C" int hj_trace_noalloc(hj_ctx* c, const float* rays_host, uint64_t n, int any_hit, uint32_t* prim_host, float* tuv_host) {
+    if (!c || (n && !rays_host)) return HJ_ERR_INVALID;
+    if (n > (uint64_t)HJ_TRACE_NOALLOC_MAX_RAYS) {
+        char b[200]; snprintf(b, sizeof b, "hj_trace_noalloc: %llu rays exceed the fixed scratch of HJ_TRACE_NOALLOC_MAX_RAYS = %d rays per call; split the batch or use hj_trace",
+                              (unsigned long long)n, (int)HJ_TRACE_NOALLOC_MAX_RAYS);
+        c->err = b; return HJ_ERR_INVALID;
+    }
+    if (c->device < 0 || c->device >= HJ_NOALLOC_MAX_DEVICES) { c->err = "hj_trace_noalloc: device index beyond the per-device table"; return HJ_ERR_INVALID; }
+    if (c->bvh.pending_set >= 0) { c->err = "hj_trace_noalloc: an asynchronous accel build is pending; call hj_accel_wait first (completing it may allocate)"; return HJ_ERR_NO_ACCEL; }
+    if (!c->have_accel) { c->err = "hj_trace_noalloc: hj_accel_build has not been called"; return HJ_ERR_NO_ACCEL; }
+    if (n == 0) return HJ_OK;
+    HJ_CUDA(c, cudaSetDevice(c->device));
+    unsigned char* base = nullptr;
+    {   // set-up, once per device, with that device current
+        std::lock_guard<std::mutex> lock(g_trace_noalloc_mutex);
+        if (!g_trace_noalloc_ptr[c->device]) {
+            void* p = nullptr;
+            HJ_CUDA(c, cudaGetSymbolAddress(&p, g_trace_noalloc_scratch));
+            g_trace_noalloc_ptr[c->device] = (unsigned char*)p;
+        }
+        base = g_trace_noalloc_ptr[c->device];
+    }
+    uint32_t* cursor = (uint32_t*)base;
+    float4* d_rays = (float4*)(base + 256);
+    uint32_t* d_prim = (uint32_t*)(base + 256 + (size_t)HJ_TRACE_NOALLOC_MAX_RAYS * 32);
+    float* d_tuv = (float*)(base + 256 + (size_t)HJ_TRACE_NOALLOC_MAX_RAYS * 36);
+    HJ_CUDA(c, cudaMemsetAsync(cursor, 0, 256, c->stream));             // the one thing that must start at zero
+    HJ_CUDA(c, cudaMemcpyAsync(d_rays, rays_host, n * 32, cudaMemcpyHostToDevice, c->stream));
+    int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    const uint32_t grid = (uint32_t)std::min<uint64_t>((n + HJ_TRACE_THREADS - 1) / HJ_TRACE_THREADS, (uint64_t)sms * HJ_MINB);
+    if (any_hit) k_trace_batch<true><<<grid, HJ_TRACE_THREADS, 0, c->stream>>>(c->S, d_rays, (uint32_t)n, d_prim, d_tuv, cursor);
+    else k_trace_batch<false><<<grid, HJ_TRACE_THREADS, 0, c->stream>>>(c->S, d_rays, (uint32_t)n, d_prim, d_tuv, cursor);
+    if (prim_host) HJ_CUDA(c, cudaMemcpyAsync(prim_host, d_prim, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (tuv_host && !any_hit) HJ_CUDA(c, cudaMemcpyAsync(tuv_host, d_tuv, n * 12, cudaMemcpyDeviceToHost, c->stream));
     HJ_CUDA(c, cudaStreamSynchronize(c->stream));
     HJ_CUDA(c, cudaGetLastError());
     return HJ_OK;

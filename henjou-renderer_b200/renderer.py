@@ -48,6 +48,7 @@ def load_library():
     L.hj_finalize.argtypes = [vp]
     L.hj_get_stats.argtypes = [vp, C.POINTER(abi.hj_stats)]
     L.hj_trace.argtypes = [vp, abi.f32p, C.c_uint64, C.c_int, abi.u32p, abi.f32p]
+    L.hj_trace_noalloc.argtypes = [vp, abi.f32p, C.c_uint64, C.c_int, abi.u32p, abi.f32p]
     L.hj_post.argtypes = [vp, C.c_int]
     L.hj_libm_eval.argtypes = [vp, C.c_int, abi.f32p, abi.f32p, abi.f32p, C.c_uint64]
     L.hj_host_pin.argtypes = [vp, vp, C.c_size_t]
@@ -155,6 +156,17 @@ class Renderer:
         tuv = np.zeros((n, 3), np.float32)
         self._check(self.L.hj_trace(self.ctx, rays.ctypes.data_as(abi.f32p), n, int(any_hit), prim.ctypes.data_as(abi.u32p),
                                     tuv.ctypes.data_as(abi.f32p)), "hj_trace")
+        return prim, tuv
+
+    def trace_noalloc(self, rays, any_hit=False):
+        """hj_trace_noalloc: the batch ray query on the library's fixed device scratch (no cudaMalloc; at most
+        abi.TRACE_NOALLOC_MAX_RAYS rays per call)."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        n = rays.shape[0]
+        prim = np.zeros(n, np.uint32)
+        tuv = np.zeros((n, 3), np.float32)
+        self._check(self.L.hj_trace_noalloc(self.ctx, rays.ctypes.data_as(abi.f32p), n, int(any_hit), prim.ctypes.data_as(abi.u32p),
+                                            tuv.ctypes.data_as(abi.f32p)), "hj_trace_noalloc")
         return prim, tuv
 
     LIBM_FN = {"sinf": 0, "cosf": 1, "acosf": 2, "logf": 3, "expf": 4, "powf": 5, "atan2f": 6}

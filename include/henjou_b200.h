@@ -249,6 +249,20 @@ int hj_trace(hj_ctx* ctx, const float* rays, uint64_t n, int any_hit, uint32_t* 
  * color.h:10-29, renderer.h:73-85); the same header compiled for the host gives the same bits (tests/test_gpu_libm.py). */
 int hj_libm_eval(hj_ctx* ctx, int fn, const float* a, const float* b, float* out, uint64_t n);
 
+/* hj_trace without any device allocation. NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Same arguments, same results
+ * (bit for bit) as hj_trace, but the device staging of rays / results and the kernel's work-fetch cursor live in one fixed
+ * `static __device__` array inside the library (about 3 MB; every GPU that loads the library holds it until the process exits) instead
+ * of buffers the context grows with cudaMalloc. It calls no cudaMalloc, no cudaFree and no allocating library routine.
+ *   - at most HJ_TRACE_NOALLOC_MAX_RAYS rays per call; more is refused with HJ_ERR_INVALID and a message (split the batch);
+ *   - an acceleration structure must be in place and no hj_accel_build_async may be pending (HJ_ERR_NO_ACCEL otherwise: completing a
+ *     pending build may allocate);
+ *   - all calls on one GPU share the array: calls that overlap on the GPU (two contexts, streams or threads) race. The call is
+ *     synchronous, so calls made one after the other never overlap. The array keeps the previous call's contents; what must start at
+ *     zero is cleared by every call. */
+#define HJ_TRACE_NOALLOC_MAX_RAYS 65536
+int hj_trace_noalloc(hj_ctx* ctx, const float* rays, uint64_t n, int any_hit, uint32_t* prim, float* tuv);
+
 /* Multi-GPU: sample-slice data parallelism, replicated scene, one sum-reduction of the
  * float4 accumulation buffer per frame over NCCL/NVLink. unique_id is the 128-byte ncclUniqueId. */
 int hj_comm_unique_id(void* unique_id_128);
