@@ -193,6 +193,7 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SURF_MINB) k_surface(DevScene S
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
         const uint32_t slot = (i < n) ? P.q_ext[cur][i] : 0xffffffffu;
+        // (r02: starting the NEXT iteration's gather chain with prefetch.global.L2 here was measured: shading 127 -> 132 ms)
         int cls = -1;
         if (slot != 0xffffffffu) {
             const float4 hq = P.hit[slot];
@@ -288,8 +289,82 @@ HJ_DI float3 sample_class(const DevScene& S, const Surface& prd, const float3& l
 // so that a warp fetches each instruction of the 50 KB sampling code once for 16 surfaces x 2 samples — instruction-cache misses are
 // this kernel's top stall. Same bits, but no gain: serial shading 124.5 -> 130 ms per C2 frame (twice the queue reads and surface-record
 // loads, and the two lanes' epilogues diverge).
+// HJ_SAMPLE_SYNC (r02): blocks of HJ_SAMPLE_THREADS threads whose warps pass through the three phases of an iteration (light sample /
+// MIS sample / continuation sample) TOGETHER, separated by __syncthreads(), so that the 16 warps of a block fetch the same region of the
+// 88 KB of code at the same time: instruction-cache misses were this kernel's top stall (ncu no_instruction 5.0 cycles per issue at 0.38
+// IPC). Same arithmetic, same bits. Serial shading per C2 frame: 127.0 ms without -> 121.4 (128 threads) / 116.5 (256) / 113.6 (512) /
+// 117.3 (1024); frame 361.4 -> 346.3 ms, C5 549 -> 536, C3 514 -> 512. The block size alone does nothing (256 threads, no barriers:
+// 126.6). Also measured and dropped: one more barrier between the state load and the light sample (113.7), and a barrier between
+// choosing the direction and evaluating the BSDF inside each sample (119.9: the extra live state and barrier waits cost more).
+#ifndef HJ_SAMPLE_SYNC
+#define HJ_SAMPLE_SYNC 1
+#endif
+#ifndef HJ_SAMPLE_THREADS
+#define HJ_SAMPLE_THREADS 512
+#endif
+#define HJ_SAMPLE_MINB ((HJ_SHADE_MINB * WF_THREADS) / HJ_SAMPLE_THREADS)
+#if HJ_SAMPLE_SYNC
 template <int INTEG, int CLS>
-__global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
+__global__ void __launch_bounds__(HJ_SAMPLE_THREADS, HJ_SAMPLE_MINB) k_sample(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
+    const uint32_t n = P.cnt->n_cls[CLS];
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i - threadIdx.x) < n; i += stride) {      // block-uniform trip count
+        const uint32_t slot = (i < n) ? P.q_cls[CLS][i] : 0xffffffffu;
+        const bool valid = slot != 0xffffffffu;
+        bool push_mis = false, push_next = false, push_shadow = false, push_sky = false;
+        Surface prd{}; float3 thr = f3(0.0f), t = f3(0.0f), b = f3(0.0f), nrm = f3(0.0f), lwo = f3(0.0f);
+        Sampler st; st.n_spp = 0; st.scramble = F.frame; st.image_idx = 0; st.depth = 0;
+        if (valid) {
+            prd = load_surface(P, slot);
+            const float3 d = f3(P.ray_d[slot]);
+            thr = f3(P.thr[slot]);
+            st.n_spp = s0 + slot / F.npix; st.image_idx = F.pix0 + slot % F.npix; st.depth = P.rng[slot];
+            nrm = prd.normal;
+            onb(nrm, t, b);
+            lwo = to_local(-d, t, nrm, b);
+            if (INTEG != HJ_INTEGRATOR_PT && CLS != HJ_CLS_GLASS) nee_stage<INTEG>(S, F, P, slot, prd, thr, lwo, t, nrm, b, st, push_shadow, push_sky);
+            else {
+                if (INTEG != HJ_INTEGRATOR_PT && S.n_lights >= 1) st.depth += 2;
+                if (INTEG == HJ_INTEGRATOR_MIS && F.sky) st.depth += 1;
+            }
+            if (INTEG == HJ_INTEGRATOR_NEE) draw_skip(st);
+        }
+#pragma unroll 1
+        for (int k = (INTEG == HJ_INTEGRATOR_MIS ? 0 : 1); k < 2; k++) {
+            __syncthreads();
+            if (valid) {
+                float pdf = 1.0f;
+                float3 lwi = f3(0.0f, 1.0f, 0.0f);
+                const float3 f = sample_class<CLS>(S, prd, lwo, lwi, pdf, st);
+                const float3 wi = to_world(lwi, t, nrm, b);
+                if (k == 0) {
+                    const float c1 = absdot(wi, nrm);
+                    if (!is_zero3(f * c1)) {
+                        push_mis = true;
+                        P.mi_o[slot] = f4(prd.position, c1); P.mi_d[slot] = f4(wi, pdf);
+                        P.mi_a[slot] = f4(f, prd.is_specular ? 1.0f : 0.0f); P.mi_t[slot] = f4(thr, 0.0f);
+                    }
+                    draw_skip(st);
+                } else {
+                    thr *= f * fabsf(dot(wi, nrm)) / pdf;
+                    if (depth + 1 < F.max_depth && roulette(thr, st)) {
+                        push_next = true;
+                        P.ray_o[slot] = f4(prd.position, 0.0f); P.ray_d[slot] = f4(wi, 0.0f);
+                        P.thr[slot] = f4(thr, 0.0f); P.rng[slot] = st.depth;
+                    }
+                }
+            }
+        }
+        if (INTEG != HJ_INTEGRATOR_PT && CLS != HJ_CLS_GLASS) queue_push(&P.cnt->n_shadow, P.q_shadow, push_shadow, slot);
+        if (INTEG == HJ_INTEGRATOR_MIS && CLS != HJ_CLS_GLASS && F.sky) queue_push(&P.cnt->n_sky, P.q_sky, push_sky, slot);
+        if (INTEG == HJ_INTEGRATOR_MIS) queue_push(&P.cnt->n_mis, P.q_mis, push_mis, slot);
+        queue_push(&P.cnt->n_extend[cur ^ 1], P.q_ext[cur ^ 1], push_next, slot);
+        __syncthreads();
+    }
+}
+#else
+template <int INTEG, int CLS>
+__global__ void __launch_bounds__(HJ_SAMPLE_THREADS, HJ_SAMPLE_MINB) k_sample(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
     const uint32_t n = P.cnt->n_cls[CLS];
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < n; i += stride) {
@@ -339,6 +414,7 @@ __global__ void __launch_bounds__(WF_THREADS, HJ_SHADE_MINB) k_sample(DevScene S
         queue_push(&P.cnt->n_extend[cur ^ 1], P.q_ext[cur ^ 1], push_next, slot);
     }
 }
+#endif
 // ---------------------------------------------------------------------------------------------- traversal kernels
 // One persistent kernel per ray type (the reference's two optixTrace call sites, rt.h:53 RayTrace and rt.h:25
 // TraceOcculution, plus the MIS emitter ray rt.h:389). Warps fetch rays from the queue dynamically: a lane whose ray
@@ -644,9 +720,10 @@ template <int INTEG>
 static int launch_shade_t(hj_ctx* c, uint32_t grid, cudaStream_t ps, const FrameK& F, const WfPtrs& P, int cur, int depth, uint32_t s0) {
     int n = 4;
     k_surface<INTEG><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
-    k_sample<INTEG, HJ_CLS_DISNEY><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
-    k_sample<INTEG, HJ_CLS_GGX><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
-    k_sample<INTEG, HJ_CLS_GLASS><<<grid, WF_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+    const uint32_t sgrid = std::max(1u, grid * WF_THREADS / HJ_SAMPLE_THREADS);      // same number of threads as the other shading kernels
+    k_sample<INTEG, HJ_CLS_DISNEY><<<sgrid, HJ_SAMPLE_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+    k_sample<INTEG, HJ_CLS_GGX><<<sgrid, HJ_SAMPLE_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
+    k_sample<INTEG, HJ_CLS_GLASS><<<sgrid, HJ_SAMPLE_THREADS, 0, ps>>>(c->S, F, P, cur, depth, s0);
     return n;
 }
 static int launch_shade(hj_ctx* c, int integrator, uint32_t grid, cudaStream_t ps, const FrameK& F, const WfPtrs& P, int cur, int depth, uint32_t s0) {
