@@ -294,7 +294,8 @@ HJ_DI float3 sample_class(const DevScene& S, const Surface& prd, const float3& l
 // 88 KB of code at the same time: instruction-cache misses were this kernel's top stall (ncu no_instruction 5.0 cycles per issue at 0.38
 // IPC). Same arithmetic, same bits. Serial shading per C2 frame: 127.0 ms without -> 121.4 (128 threads) / 116.5 (256) / 113.6 (512) /
 // 117.3 (1024); frame 361.4 -> 346.3 ms, C5 549 -> 536, C3 514 -> 512. The block size alone does nothing (256 threads, no barriers:
-// 126.6). Also measured and dropped: one more barrier between the state load and the light sample (113.7), and a barrier between
+// 126.6); other block shapes with barriers: 512 x 1 block (128 registers, no spills) 125.4, 768 x 1 (80 registers) 122.6, 384 x 2 (80) 117.7.
+// ncu after the change: no_instruction 5.0 -> 0.3-0.9 cycles per issue, barrier 1.9-4.1 (profiles/r02_ncu_shading_c2.txt). Also measured and dropped: one more barrier between the state load and the light sample (113.7), and a barrier between
 // choosing the direction and evaluating the BSDF inside each sample (119.9: the extra live state and barrier waits cost more).
 #ifndef HJ_SAMPLE_SYNC
 #define HJ_SAMPLE_SYNC 1
@@ -302,7 +303,9 @@ HJ_DI float3 sample_class(const DevScene& S, const Surface& prd, const float3& l
 #ifndef HJ_SAMPLE_THREADS
 #define HJ_SAMPLE_THREADS 512
 #endif
+#ifndef HJ_SAMPLE_MINB
 #define HJ_SAMPLE_MINB ((HJ_SHADE_MINB * WF_THREADS) / HJ_SAMPLE_THREADS)
+#endif
 #if HJ_SAMPLE_SYNC
 template <int INTEG, int CLS>
 __global__ void __launch_bounds__(HJ_SAMPLE_THREADS, HJ_SAMPLE_MINB) k_sample(DevScene S, FrameK F, WfPtrs P, int cur, int depth, uint32_t s0) {
