@@ -229,9 +229,11 @@ def gpu_arm(args, rank, world, local_rank):
             return float(tmax[0]), int(tsum[1]), int(tsum[2]), wall, (float(tmin[3]) / steps, float(tmax[3]) / steps)
         return t_rank, rays, launches, wall, (dev_ms / steps, dev_ms / steps)
 
-    clocks = ClockSampler(local_rank)
+    # only rank 0's record is reported: one nvidia-smi poller per box, not one per rank (its queries perturb the driver; r02: at N = 2 / 4
+    # single steps of 258 instead of 175 ms / 100 instead of 89 ms with a poller on every rank)
+    clocks = ClockSampler(local_rank) if rank == 0 else None
     t_all, rays_all, launches_all, wall, render_ms = timed(fp, args.steps, args.warmup)
-    clk = clocks.stop()
+    clk = clocks.stop() if clocks else None
     value = rays_all / t_all / 1e6
     out = dict(metric="Mrays/s", value=round(value, 2), unit="Mrays/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
                ms_per_step=round(1e3 * t_all / args.steps, 3), higher_is_better=True, scaling="strong" if strong else "weak", vs_baseline=None, dtype="f32",
