@@ -104,6 +104,8 @@ void hj_destroy(hj_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    if (c->bvh.build_stream) cudaStreamSynchronize(c->bvh.build_stream);     // a build enqueued by hj_accel_build_async may still be writing the buffers freed below
+    for (WavefrontState& w : c->wf) if (w.stream) cudaStreamSynchronize(w.stream);
     hj_comm_destroy_internal(c);
     DevBuf* bufs[] = {&c->d_vertices, &c->d_normals, &c->d_texcoords, &c->d_indices, &c->d_material_ids, &c->d_prim_offsets, &c->d_tri_inst,
                       &c->d_materials, &c->d_textures, &c->d_texels, &c->d_srgb, &c->d_light_ids, &c->d_light_em,
